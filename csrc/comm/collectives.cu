@@ -1,0 +1,443 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch.
+//
+// Every rank maps every other rank's symmetric heap (see symm.cu), so a
+// collective is ONE kernel per rank that loads from / stores to peer addresses
+// directly.  Ranks meet at flag barriers kept in a per-rank signal pad:
+// rank s tells rank d "I reached step q of block b on channel c" by storing q
+// (st.release.sys) into d's pad at [c][b][s]; d spins with ld.acquire.sys.
+// Sequence numbers only grow (the next value is kept in the pad as well), so
+// flags are never reset and back-to-back launches cannot confuse each other.
+// A bounded spin turns a dead peer into an error flag instead of a GPU hang.
+//
+//   all-reduce (two-shot)   rank r reduces slice r from all peers in fixed rank
+//                           order (fp32), scales by 1/W, casts, and stores the
+//                           result into every peer's buffer: NCCL all-reduce +
+//                           div_ + dtype cast in one pass.
+//   all-reduce (one-shot)   small buffers: every rank reduces everything locally.
+//   broadcast               root stores its bytes into every peer (K2/K3).
+//   all-gather              every rank stores its shard into every peer (K6/K8).
+//   reduce-scatter          owner pulls its slice from all peers (K7).
+//   rs_optim                reduce-scatter fused with SGD / AdamW on the fp32
+//                           master shard and the bf16 shard write-back (K7+K13).
+//
+// Reference call sites: dist.broadcast / dist.all_reduce in
+// /root/reference/src/playground/ddp_script.py:120-121,149-154 and the implicit
+// NCCL collectives of torch DDP / FSDP (ddp_strategy.py:18, fsdp_strategy.py:20).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "../../include/dtb200.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dtb {
+namespace comm {
+
+constexpr int MAX_BLOCKS = 64;       // barrier slots per channel
+constexpr int NUM_CHANNELS = 16;
+constexpr int THREADS = 512;
+// signal pad layout (uint32 slots)
+constexpr int FLAG_SLOTS = NUM_CHANNELS * MAX_BLOCKS * DTB_MAX_RANKS;   // 8192
+constexpr int SEQ_BASE = FLAG_SLOTS;                                     // [channel][block] next sequence
+constexpr int ERR_SLOT = DTB_SIGNAL_PAD_BYTES / 4 - 1;
+constexpr long long DEFAULT_TIMEOUT = 40000000000LL;                     // ~20 s of SM clocks
+
+struct Ctx {
+  dtb_comm c;
+  int channel;
+};
+
+__device__ __forceinline__ int flag_slot(int channel, int block, int src_rank) {
+  return (channel * MAX_BLOCKS + block) * DTB_MAX_RANKS + src_rank;
+}
+
+// Block-level barrier across ranks.  All threads of the block call it; on return
+// every peer's block with the same index has arrived and its earlier stores are
+// visible here.  `seq` is this block's running sequence number (register copy).
+__device__ __forceinline__ void rank_barrier(const Ctx& x, uint32_t& seq) {
+  __syncthreads();
+  seq += 1;
+  if (threadIdx.x < static_cast<unsigned>(x.c.world)) {
+    const int peer = threadIdx.x;
+    st_release_sys(x.c.signals[peer] + flag_slot(x.channel, blockIdx.x, x.c.rank), seq);
+    const uint32_t* mine = x.c.signals[x.c.rank] + flag_slot(x.channel, blockIdx.x, peer);
+    const long long limit = x.c.timeout_cycles > 0 ? x.c.timeout_cycles : DEFAULT_TIMEOUT;
+    const long long t0 = clock64();
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - seq) < 0) {
+      if (clock64() - t0 > limit) {
+        x.c.signals[x.c.rank][ERR_SLOT] = 1u + static_cast<uint32_t>(peer);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t load_seq(const Ctx& x) {
+  return x.c.signals[x.c.rank][SEQ_BASE + x.channel * MAX_BLOCKS + blockIdx.x];
+}
+__device__ __forceinline__ void store_seq(const Ctx& x, uint32_t seq) {
+  if (threadIdx.x == 0) x.c.signals[x.c.rank][SEQ_BASE + x.channel * MAX_BLOCKS + blockIdx.x] = seq;
+}
+
+// ---- vector helpers ---------------------------------------------------------
+template <bool FP32>
+struct Vec;   // 16 bytes of elements as floats
+
+template <>
+struct Vec<false> {
+  static constexpr int N = 8;
+  __device__ static void unpack(const uint4& r, float* f) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 t = __bfloat1622float2(h[i]);
+      f[2 * i] = t.x;
+      f[2 * i + 1] = t.y;
+    }
+  }
+  __device__ static uint4 pack(const float* f) {
+    uint4 r;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return r;
+  }
+};
+template <>
+struct Vec<true> {
+  static constexpr int N = 4;
+  __device__ static void unpack(const uint4& r, float* f) {
+    f[0] = __uint_as_float(r.x); f[1] = __uint_as_float(r.y); f[2] = __uint_as_float(r.z); f[3] = __uint_as_float(r.w);
+  }
+  __device__ static uint4 pack(const float* f) {
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+  }
+};
+
+// Sum of the same 16-byte vector on every rank, fixed order 0..W-1, all loads in flight first.
+template <bool FP32, int W>
+__device__ __forceinline__ void reduce_vec(const Ctx& x, size_t byte_off, float* acc) {
+  uint4 raw[W];
+#pragma unroll
+  for (int r = 0; r < W; ++r) raw[r] = ld_volatile_v4(static_cast<const uint8_t*>(x.c.peers[r]) + byte_off);
+#pragma unroll
+  for (int j = 0; j < Vec<FP32>::N; ++j) acc[j] = 0.f;
+#pragma unroll
+  for (int r = 0; r < W; ++r) {
+    float f[Vec<FP32>::N];
+    Vec<FP32>::unpack(raw[r], f);
+#pragma unroll
+    for (int j = 0; j < Vec<FP32>::N; ++j) acc[j] += f[j];
+  }
+}
+
+// ---- kernels ------------------------------------------------------------------
+__global__ void __launch_bounds__(THREADS) barrier_kernel(const Ctx x) {
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);
+  store_seq(x, seq);
+}
+
+// Two-shot in-place mean.  nvec = number of 16-byte vectors in the buffer.
+template <bool FP32, int W>
+__global__ void __launch_bounds__(THREADS) allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec) {
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);   // every rank's gradients are final
+  const long long lo = nvec * x.c.rank / W, hi = nvec * (x.c.rank + 1) / W;
+  const float scale = 1.f / W;
+  for (long long v = lo + static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < hi;
+       v += static_cast<long long>(gridDim.x) * THREADS) {
+    float acc[Vec<FP32>::N];
+    const size_t off = offset + static_cast<size_t>(v) * 16;
+    reduce_vec<FP32, W>(x, off, acc);
+#pragma unroll
+    for (int j = 0; j < Vec<FP32>::N; ++j) acc[j] *= scale;
+    const uint4 out = Vec<FP32>::pack(acc);
+#pragma unroll
+    for (int r = 0; r < W; ++r) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + off, out);
+  }
+  rank_barrier(x, seq);   // every slice has been delivered to this rank
+  store_seq(x, seq);
+}
+
+// One-shot in-place mean for small buffers: each rank reduces the whole buffer into
+// registers, all ranks meet (nobody may overwrite data a peer still reads), then store.
+template <bool FP32, int W, int PER_THREAD>
+__global__ void __launch_bounds__(THREADS) allreduce_oneshot_kernel(const Ctx x, size_t offset, long long nvec) {
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);
+  float acc[PER_THREAD][Vec<FP32>::N];
+  const long long base = static_cast<long long>(blockIdx.x) * THREADS * PER_THREAD + threadIdx.x;
+  const float scale = 1.f / W;
+#pragma unroll
+  for (int i = 0; i < PER_THREAD; ++i) {
+    const long long v = base + static_cast<long long>(i) * THREADS;
+    if (v < nvec) reduce_vec<FP32, W>(x, offset + static_cast<size_t>(v) * 16, acc[i]);
+  }
+  rank_barrier(x, seq);
+#pragma unroll
+  for (int i = 0; i < PER_THREAD; ++i) {
+    const long long v = base + static_cast<long long>(i) * THREADS;
+    if (v < nvec) {
+#pragma unroll
+      for (int j = 0; j < Vec<FP32>::N; ++j) acc[i][j] *= scale;
+      st_v4(static_cast<uint8_t*>(x.c.peers[x.c.rank]) + offset + static_cast<size_t>(v) * 16, Vec<FP32>::pack(acc[i]));
+    }
+  }
+  store_seq(x, seq);
+}
+
+__global__ void __launch_bounds__(THREADS) broadcast_kernel(const Ctx x, size_t offset, long long nvec, int root) {
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);   // destinations are free to be overwritten
+  if (x.c.rank == root) {
+    const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[root]) + offset;
+    for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec;
+         v += static_cast<long long>(gridDim.x) * THREADS) {
+      const uint4 val = *reinterpret_cast<const uint4*>(src + v * 16);
+      for (int r = 0; r < x.c.world; ++r)
+        if (r != root) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + offset + v * 16, val);
+    }
+  }
+  rank_barrier(x, seq);
+  store_seq(x, seq);
+}
+
+// Push all-gather: rank r stores its shard (nvec vectors at src_off) to dst_off + r*shard on every rank.
+__global__ void __launch_bounds__(THREADS) allgather_kernel(const Ctx x, size_t dst_off, size_t src_off, long long nvec) {
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);
+  const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[x.c.rank]) + src_off;
+  const size_t slot = dst_off + static_cast<size_t>(x.c.rank) * static_cast<size_t>(nvec) * 16;
+  for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec;
+       v += static_cast<long long>(gridDim.x) * THREADS) {
+    const uint4 val = *reinterpret_cast<const uint4*>(src + v * 16);
+    for (int r = 0; r < x.c.world; ++r) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + slot + v * 16, val);
+  }
+  rank_barrier(x, seq);
+  store_seq(x, seq);
+}
+
+struct OptArgs {
+  float* master; float* m; float* v;
+  __nv_bfloat16* shard;       // local bf16 shard (in the symmetric heap)
+  int opt;                    // 0 sgd, 1 adamw
+  float lr, beta1, beta2, eps, wd, bc1, bc2, momentum;
+};
+
+// Reduce-scatter (mean) of slice `rank`; MODE 0: write fp32/bf16 result to `out`; MODE 1: fused optimizer.
+template <bool FP32, int W, int MODE>
+__global__ void __launch_bounds__(THREADS)
+reduce_scatter_kernel(const Ctx x, size_t src_off, long long nvec, void* out, int out_fp32, const OptArgs o) {
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);
+  const size_t slice = src_off + static_cast<size_t>(x.c.rank) * static_cast<size_t>(nvec) * 16;
+  const float scale = 1.f / W;
+  constexpr int N = Vec<FP32>::N;
+  for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec;
+       v += static_cast<long long>(gridDim.x) * THREADS) {
+    float g[N];
+    reduce_vec<FP32, W>(x, slice + static_cast<size_t>(v) * 16, g);
+#pragma unroll
+    for (int j = 0; j < N; ++j) g[j] *= scale;
+    const long long e = v * N;
+    if (MODE == 0) {
+      if (out_fp32) {
+#pragma unroll
+        for (int j = 0; j < N; j += 4)
+          *reinterpret_cast<float4*>(static_cast<float*>(out) + e + j) = make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]);
+      } else {
+        __nv_bfloat16* ob = static_cast<__nv_bfloat16*>(out) + e;
+#pragma unroll
+        for (int j = 0; j < N; j += 2) *reinterpret_cast<__nv_bfloat162*>(ob + j) = __floats2bfloat162_rn(g[j], g[j + 1]);
+      }
+    } else {
+      float w[N];
+#pragma unroll
+      for (int j = 0; j < N; j += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(o.master + e + j);
+        w[j] = t.x; w[j + 1] = t.y; w[j + 2] = t.z; w[j + 3] = t.w;
+      }
+      if (o.opt == 1) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          float m = o.m[e + j], vv = o.v[e + j];
+          m = o.beta1 * m + (1.f - o.beta1) * g[j];
+          vv = o.beta2 * vv + (1.f - o.beta2) * g[j] * g[j];
+          o.m[e + j] = m;
+          o.v[e + j] = vv;
+          w[j] = w[j] * (1.f - o.lr * o.wd) - o.lr * (m / o.bc1) / (sqrtf(vv / o.bc2) + o.eps);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          float d = g[j] + o.wd * w[j];
+          if (o.m != nullptr) {
+            d = o.momentum * o.m[e + j] + d;
+            o.m[e + j] = d;
+          }
+          w[j] -= o.lr * d;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < N; j += 4)
+        *reinterpret_cast<float4*>(o.master + e + j) = make_float4(w[j], w[j + 1], w[j + 2], w[j + 3]);
+#pragma unroll
+      for (int j = 0; j < N; j += 2)
+        *reinterpret_cast<__nv_bfloat162*>(o.shard + e + j) = __floats2bfloat162_rn(w[j], w[j + 1]);
+    }
+  }
+  rank_barrier(x, seq);   // peers may reuse their gradient buffers only after every owner has read them
+  store_seq(x, seq);
+}
+
+// ---- host dispatch --------------------------------------------------------------
+static int pick_grid(long long nvec, int max_ctas, int dflt) {
+  int cap = max_ctas > 0 ? max_ctas : dflt;
+  if (cap > MAX_BLOCKS) cap = MAX_BLOCKS;
+  long long need = (nvec + THREADS - 1) / THREADS;
+  if (need < 1) need = 1;
+  return static_cast<int>(need < cap ? need : cap);
+}
+
+static int check(const dtb_comm* c, int channel) {
+  DTB_REQUIRE(c != nullptr && c->world >= 1 && c->world <= DTB_MAX_RANKS && c->rank >= 0 && c->rank < c->world,
+              "dtb_comm: bad communicator");
+  DTB_REQUIRE(channel >= 0 && channel < NUM_CHANNELS, "dtb_comm: channel %d out of range", channel);
+  return 0;
+}
+
+#define DISPATCH_W(W_, ...)                 \
+  switch (W_) {                             \
+    case 1: { constexpr int W = 1; __VA_ARGS__; break; } \
+    case 2: { constexpr int W = 2; __VA_ARGS__; break; } \
+    case 4: { constexpr int W = 4; __VA_ARGS__; break; } \
+    case 8: { constexpr int W = 8; __VA_ARGS__; break; } \
+    default: dtb::set_error("dtb_comm: world size %d not supported (1, 2, 4, 8)", W_); return 2; \
+  }
+
+}  // namespace comm
+}  // namespace dtb
+
+using namespace dtb;
+using namespace dtb::comm;
+
+// The channel rides in the upper bits of max_ctas (bits 16..19) so the public signatures stay small.
+static inline int channel_of(int max_ctas) { return (max_ctas >> 16) & 0xF; }
+static inline int ctas_of(int max_ctas) { return max_ctas & 0xFFFF; }
+
+extern "C" int dtb_comm_barrier(const dtb_comm* c, int channel, void* stream) {
+  if (check(c, channel)) return 2;
+  Ctx x = {*c, channel};
+  barrier_kernel<<<1, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes, int root, int max_ctas,
+                                  void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  DTB_REQUIRE(offset % 16 == 0 && bytes % 16 == 0, "dtb_comm_broadcast: offset/bytes must be multiples of 16");
+  if (bytes == 0) return 0;
+  Ctx x = {*c, channel_of(max_ctas)};
+  const long long nvec = static_cast<long long>(bytes / 16);
+  broadcast_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 32), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, offset, nvec,
+                                                                                                        root);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long long n, int dtype, int algo, int max_ctas,
+                                       void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  const int esize = dtype == 1 ? 4 : 2;
+  DTB_REQUIRE(offset % 16 == 0 && (n * esize) % 16 == 0, "dtb_comm_all_reduce_avg: buffer must be 16-byte granular");
+  DTB_REQUIRE(algo != 3, "dtb_comm_all_reduce_avg: NVLS multimem path is not mapped in this build");
+  if (n == 0) return 0;
+  Ctx x = {*c, channel_of(max_ctas)};
+  const long long nvec = n * esize / 16;
+  auto s = static_cast<cudaStream_t>(stream);
+  constexpr int PT = 4;
+  const long long oneshot_cap = 64LL * 1024 / 16;   // <= 64 KiB
+  if (algo == 0) algo = (nvec <= oneshot_cap) ? 1 : 2;
+  if (algo == 1) {
+    const long long per_block = static_cast<long long>(THREADS) * PT;
+    const long long blocks = (nvec + per_block - 1) / per_block;
+    DTB_REQUIRE(blocks <= MAX_BLOCKS, "dtb_comm_all_reduce_avg: one-shot limited to %lld bytes",
+                per_block * MAX_BLOCKS * 16);
+    DISPATCH_W(c->world, {
+      if (dtype == 1) allreduce_oneshot_kernel<true, W, PT><<<static_cast<int>(blocks), THREADS, 0, s>>>(x, offset, nvec);
+      else allreduce_oneshot_kernel<false, W, PT><<<static_cast<int>(blocks), THREADS, 0, s>>>(x, offset, nvec);
+    });
+  } else {
+    const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 32);
+    DISPATCH_W(c->world, {
+      if (dtype == 1) allreduce_twoshot_kernel<true, W><<<grid, THREADS, 0, s>>>(x, offset, nvec);
+      else allreduce_twoshot_kernel<false, W><<<grid, THREADS, 0, s>>>(x, offset, nvec);
+    });
+  }
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_all_gather(const dtb_comm* c, size_t dst_offset, size_t src_offset, long long n, int esize,
+                                   int max_ctas, void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  DTB_REQUIRE(dst_offset % 16 == 0 && src_offset % 16 == 0 && (n * esize) % 16 == 0,
+              "dtb_comm_all_gather: shard must be 16-byte granular");
+  if (n == 0) return 0;
+  Ctx x = {*c, channel_of(max_ctas)};
+  const long long nvec = n * esize / 16;
+  allgather_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 32), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, dst_offset, src_offset, nvec);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_reduce_scatter_avg(const dtb_comm* c, void* out, int out_fp32, size_t src_offset, long long n,
+                                           int src_dtype, int max_ctas, void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  const int esize = src_dtype == 1 ? 4 : 2;
+  DTB_REQUIRE(src_offset % 16 == 0 && (n * esize) % 16 == 0, "dtb_comm_reduce_scatter_avg: shard must be 16-byte granular");
+  if (n == 0) return 0;
+  Ctx x = {*c, channel_of(max_ctas)};
+  const long long nvec = n * esize / 16;
+  const int grid = pick_grid(nvec, ctas_of(max_ctas), 32);
+  auto s = static_cast<cudaStream_t>(stream);
+  OptArgs o = {};
+  DISPATCH_W(c->world, {
+    if (src_dtype == 1) reduce_scatter_kernel<true, W, 0><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
+    else reduce_scatter_kernel<false, W, 0><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
+  });
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t shard_offset, float* master, float* m,
+                                 float* v, long long n, int opt, float lr, float beta1, float beta2, float eps,
+                                 float weight_decay, float bias_corr1, float bias_corr2, float momentum, int max_ctas,
+                                 void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  DTB_REQUIRE(grad_offset % 16 == 0 && shard_offset % 16 == 0 && n % 8 == 0, "dtb_comm_rs_optim: shard must be 16-byte granular");
+  DTB_REQUIRE(master != nullptr, "dtb_comm_rs_optim: fp32 master shard is required");
+  DTB_REQUIRE(opt == 0 || (m != nullptr && v != nullptr), "dtb_comm_rs_optim: AdamW needs both moments");
+  if (n == 0) return 0;
+  Ctx x = {*c, channel_of(max_ctas)};
+  const long long nvec = n * 2 / 16;
+  const int grid = pick_grid(nvec, ctas_of(max_ctas), 32);
+  OptArgs o = {master, m, v,
+               reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(c->peers[c->rank]) + shard_offset),
+               opt, lr, beta1, beta2, eps, weight_decay, bias_corr1, bias_corr2, momentum};
+  auto s = static_cast<cudaStream_t>(stream);
+  DISPATCH_W(c->world, { reduce_scatter_kernel<false, W, 1><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, nullptr, 0, o); });
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_error_flag(const dtb_comm* c) {
+  if (c == nullptr) return -1;
+  uint32_t v = 0;
+  if (cudaMemcpy(&v, c->signals[c->rank] + ERR_SLOT, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return static_cast<int>(v);
+}

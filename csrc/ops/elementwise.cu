@@ -1,0 +1,270 @@
+// Bandwidth-bound helpers: GELU fwd/bwd, add, casts, column sums (bias gradient),
+// sum of squares (gradient-norm logging) and mean.  All use 16-byte vector
+// accesses on the aligned body and a scalar tail.
+//
+// Reference call sites: the ATen elementwise / reduction kernels behind
+// loss.backward() and torch.norm() (SURVEY K10, K15;
+// /root/reference/src/playground/ddp_script.py:155-164).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "../../include/dtb200.h"
+#include "../common/host.h"
+
+namespace dtb {
+
+__device__ __forceinline__ float gelu_f(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * x * (1.0f + t);
+}
+__device__ __forceinline__ float gelu_grad_f(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float x2 = x * x;
+  float u = k0 * (x + k1 * x * x2);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * x2);
+}
+
+struct Bf16x8 {
+  uint4 raw;
+  __device__ __forceinline__ void unpack(float (&f)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 t = __bfloat1622float2(h[i]);
+      f[2 * i] = t.x;
+      f[2 * i + 1] = t.y;
+    }
+  }
+  __device__ __forceinline__ void pack(const float (&f)[8]) {
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  }
+};
+
+enum { OP_GELU = 0, OP_GELU_BWD = 1, OP_ADD = 2 };
+
+template <int OP>
+__global__ void __launch_bounds__(256) eltwise_bf16_kernel(const __nv_bfloat16* __restrict__ a,
+                                                            const __nv_bfloat16* __restrict__ b,
+                                                            __nv_bfloat16* __restrict__ out, long long n) {
+  const long long nvec = n / 8;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    Bf16x8 va, vb, vo;
+    float fa[8], fb[8], fo[8];
+    va.raw = reinterpret_cast<const uint4*>(a)[i];
+    va.unpack(fa);
+    if (OP != OP_GELU) {
+      vb.raw = reinterpret_cast<const uint4*>(b)[i];
+      vb.unpack(fb);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (OP == OP_GELU) fo[j] = gelu_f(fa[j]);
+      if (OP == OP_GELU_BWD) fo[j] = gelu_grad_f(fa[j]) * fb[j];
+      if (OP == OP_ADD) fo[j] = fa[j] + fb[j];
+    }
+    vo.pack(fo);
+    reinterpret_cast<uint4*>(out)[i] = vo.raw;
+  }
+  if (blockIdx.x == 0) {
+    for (long long i = nvec * 8 + threadIdx.x; i < n; i += blockDim.x) {
+      float x = __bfloat162float(a[i]);
+      float y = (OP != OP_GELU) ? __bfloat162float(b[i]) : 0.f;
+      float o = OP == OP_GELU ? gelu_f(x) : (OP == OP_GELU_BWD ? gelu_grad_f(x) * y : x + y);
+      out[i] = __float2bfloat16(o);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                            long long n) {
+  const long long nvec = n / 8;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float4 lo = reinterpret_cast<const float4*>(in)[2 * i];
+    float4 hi = reinterpret_cast<const float4*>(in)[2 * i + 1];
+    Bf16x8 o;
+    float f[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    o.pack(f);
+    reinterpret_cast<uint4*>(out)[i] = o.raw;
+  }
+  if (blockIdx.x == 0)
+    for (long long i = nvec * 8 + threadIdx.x; i < n; i += blockDim.x) out[i] = __float2bfloat16(in[i]);
+}
+
+__global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ out,
+                                                            long long n) {
+  const long long nvec = n / 8;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    Bf16x8 v;
+    v.raw = reinterpret_cast<const uint4*>(in)[i];
+    float f[8];
+    v.unpack(f);
+    reinterpret_cast<float4*>(out)[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+    reinterpret_cast<float4*>(out)[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+  }
+  if (blockIdx.x == 0)
+    for (long long i = nvec * 8 + threadIdx.x; i < n; i += blockDim.x) out[i] = __bfloat162float(in[i]);
+}
+
+// Column sums of a row-major [rows, cols] bf16 matrix.  Each CTA owns 64 columns
+// (8 lanes x 8 columns) and 32 row-lanes; a shared-memory tree finishes the sum,
+// so no scratch buffer or atomics are needed and the result is deterministic.
+__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, void* __restrict__ out,
+                                                          int rows, int cols, long long ldx, int out_fp32) {
+  __shared__ float part[32][65];
+  const int cx = threadIdx.x & 7;    // column group within the CTA
+  const int ry = threadIdx.x >> 3;   // 0..31 row lane
+  const int col = blockIdx.x * 64 + cx * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (col < cols) {
+    const bool vec = (col + 8 <= cols);
+    for (int r = ry; r < rows; r += 32) {
+      const __nv_bfloat16* p = x + static_cast<long long>(r) * ldx + col;
+      if (vec) {
+        Bf16x8 v;
+        v.raw = *reinterpret_cast<const uint4*>(p);
+        float f[8];
+        v.unpack(f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      } else {
+        for (int j = 0; j < 8 && col + j < cols; ++j) acc[j] += __bfloat162float(p[j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[ry][cx * 8 + j] = acc[j];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float s = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) s += part[r][threadIdx.x];
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c < cols) {
+      if (out_fp32) reinterpret_cast<float*>(out)[c] = s;
+      else reinterpret_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16(s);
+    }
+  }
+}
+
+__device__ __forceinline__ float block_sum(float v, float* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  const int nwarps = (blockDim.x + 31) >> 5;
+  v = (threadIdx.x < nwarps) ? smem[threadIdx.x] : 0.f;
+  if (warp == 0) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  }
+  __syncthreads();
+  return v;  // valid in warp 0
+}
+
+__global__ void __launch_bounds__(256) sumsq_kernel(const void* __restrict__ x, int is_fp32, long long n,
+                                                    float* __restrict__ out) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float v = is_fp32 ? reinterpret_cast<const float*>(x)[i] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(x)[i]);
+    acc += v * v;
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) atomicAdd(out, acc);
+}
+
+__global__ void __launch_bounds__(1024) mean_f32_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) acc += x[i];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) *out = acc / static_cast<float>(n);
+}
+
+static inline int grid_for(long long work_items, int block, int per_sm = 8) {
+  long long blocks = (work_items + block - 1) / block;
+  long long cap = static_cast<long long>(sm_count()) * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace dtb
+
+using namespace dtb;
+
+extern "C" int dtb_gelu_fwd_bf16(const void* x, void* y, long long n, void* stream) {
+  if (n <= 0) return 0;
+  eltwise_bf16_kernel<OP_GELU><<<grid_for(n / 8 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), nullptr, static_cast<__nv_bfloat16*>(y), n);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_gelu_bwd_bf16(const void* x, const void* dy, void* dx, long long n, void* stream) {
+  if (n <= 0) return 0;
+  eltwise_bf16_kernel<OP_GELU_BWD><<<grid_for(n / 8 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), n);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_add_bf16(const void* a, const void* b, void* out, long long n, void* stream) {
+  if (n <= 0) return 0;
+  eltwise_bf16_kernel<OP_ADD><<<grid_for(n / 8 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), static_cast<__nv_bfloat16*>(out), n);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream) {
+  if (n <= 0) return 0;
+  cast_f32_bf16_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      in, static_cast<__nv_bfloat16*>(out), n);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream) {
+  if (n <= 0) return 0;
+  cast_bf16_f32_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(in), out, n);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_colsum_bf16(const void* x, void* out, int rows, int cols, long long ldx, int out_fp32,
+                               void* stream) {
+  DTB_REQUIRE(rows > 0 && cols > 0, "dtb_colsum_bf16: empty input");
+  DTB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "dtb_colsum_bf16: x must be 16-byte aligned");
+  colsum_bf16_kernel<<<(cols + 63) / 64, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), out, rows, cols, ldx, out_fp32);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_sumsq(const void* x, int is_fp32, long long n, float* out, void* stream) {
+  if (n <= 0) return 0;
+  sumsq_kernel<<<grid_for(n, 256, 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, is_fp32, n, out);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_mean_f32(const float* x, long long n, float* out, void* stream) {
+  DTB_REQUIRE(n > 0, "dtb_mean_f32: empty input");
+  mean_f32_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(x, n, out);
+  DTB_LAUNCH_OK();
+  return 0;
+}

@@ -1,0 +1,557 @@
+// bf16 GEMM on 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM),
+// operands staged by TMA into 128B-swizzled shared memory through an mbarrier
+// ring, persistent CTAs, warp-specialised:
+//
+//   warp 0      TMA producer (one elected lane)
+//   warp 1      TMEM allocator + MMA issuer (one elected lane; leader CTA only in pair mode)
+//   warps 2..5  epilogue: tcgen05.ld -> fp32 math (bias / GELU / GELU' / axpby) -> global
+//
+// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of
+// tile i+1.  CG=2 runs the MMA as cta_group::2 on a 2-CTA cluster (256 x BN
+// tile, each CTA stages its 128 rows of A and half of B).
+//
+// Replaces the cuBLAS calls behind nn.Linear forward/backward in the reference
+// (/root/reference/src/distributed_trainer.py:162,164).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "../../include/dtb200.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dtb {
+namespace gemm {
+
+constexpr int BM = 128;        // rows of the tile owned by one CTA
+constexpr int BK = 64;         // one 128-byte swizzle atom of bf16 along K
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int NUM_EPI_WARPS = 4;
+
+struct Params {
+  int M, N, K;
+  int batch_inner, batch;        // batch = inner * outer
+  int m_blocks, n_blocks;        // in units of (CG*BM) x BN tiles
+  int group_m;
+  void* d;
+  void* d2;
+  const void* aux;
+  const void* bias;
+  long long ldd, ld_aux;
+  long long d_si, d_so, aux_si, aux_so;
+  int d_fp32, aux_fp32, bias_fp32;
+  int act;
+  float alpha, beta;
+  uint32_t lbo_a, sbo_a, lbo_b, sbo_b;   // UMMA descriptor byte offsets
+};
+
+template <int CG, int BN>
+struct Config {
+  static constexpr int A_BYTES = BM * BK * 2;              // 16 KB per CTA
+  static constexpr int B_ROWS = BN / CG;                   // B rows staged by one CTA
+  static constexpr int B_BYTES = B_ROWS * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (STAGE_BYTES >= 48 * 1024) ? 4 : 6;
+  static constexpr int TMEM_COLS = 2 * BN;                 // two accumulator stages
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static_assert(TMEM_COLS <= 512, "TMEM has 512 columns");
+  static_assert(TMEM_COLS == 128 || TMEM_COLS == 256 || TMEM_COLS == 512, "power of two");
+};
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * x * (1.0f + t);
+}
+
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float x2 = x * x;
+  float u = k0 * (x + k1 * x * x2);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  float du = k0 * (1.0f + 3.0f * k1 * x2);
+  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__device__ __forceinline__ void tile_coords(const Params& p, int tile, int& bi, int& m_blk, int& n_blk) {
+  const int per_batch = p.m_blocks * p.n_blocks;
+  bi = tile / per_batch;
+  int t = tile - bi * per_batch;
+  const int group_size = p.group_m * p.n_blocks;
+  const int group_id = t / group_size;
+  const int first_m = group_id * p.group_m;
+  const int gm = min(p.m_blocks - first_m, p.group_m);
+  const int in_group = t - group_id * group_size;
+  m_blk = first_m + in_group % gm;
+  n_blk = in_group / gm;
+}
+
+// Epilogue for one 32-column chunk of one row.
+__device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&raw)[32], int row, int col0,
+                                               long long d_off, long long aux_off) {
+  if (row >= p.M || col0 >= p.N) return;
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) * p.alpha;
+  const bool full = (col0 + 32 <= p.N);
+
+  if (p.bias != nullptr) {
+    if (p.bias_fp32) {
+      const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (full || col0 + j < p.N) v[j] += __ldg(b + j);
+    } else {
+      const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (full || col0 + j < p.N) v[j] += __bfloat162float(b[j]);
+    }
+  }
+
+  if (p.act == 1) {
+    if (p.d2 != nullptr) {
+      __nv_bfloat16* z = reinterpret_cast<__nv_bfloat16*>(p.d2) + d_off + static_cast<long long>(row) * p.ldd + col0;
+      if (full) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 o;
+          o.x = pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+          o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+          o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+          o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+          *reinterpret_cast<uint4*>(z + 8 * q) = o;
+        }
+      } else {
+        for (int j = 0; j < 32 && col0 + j < p.N; ++j) z[j] = __float2bfloat16(v[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = gelu_tanh(v[j]);
+  } else if (p.aux != nullptr) {
+    float a[32];
+    if (p.aux_fp32) {
+      const float* ap = reinterpret_cast<const float*>(p.aux) + aux_off + static_cast<long long>(row) * p.ld_aux + col0;
+      if (full) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          float4 t = *reinterpret_cast<const float4*>(ap + 4 * q);
+          a[4 * q + 0] = t.x; a[4 * q + 1] = t.y; a[4 * q + 2] = t.z; a[4 * q + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) a[j] = (col0 + j < p.N) ? ap[j] : 0.f;
+      }
+    } else {
+      const __nv_bfloat16* ap =
+          reinterpret_cast<const __nv_bfloat16*>(p.aux) + aux_off + static_cast<long long>(row) * p.ld_aux + col0;
+      if (full) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 t = *reinterpret_cast<const uint4*>(ap + 8 * q);
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float2 f = __bfloat1622float2(h[e]);
+            a[8 * q + 2 * e] = f.x;
+            a[8 * q + 2 * e + 1] = f.y;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) a[j] = (col0 + j < p.N) ? __bfloat162float(ap[j]) : 0.f;
+      }
+    }
+    if (p.act == 2) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] *= gelu_tanh_grad(a[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] += p.beta * a[j];
+    }
+  }
+
+  if (p.d_fp32) {
+    float* dp = reinterpret_cast<float*>(p.d) + d_off + static_cast<long long>(row) * p.ldd + col0;
+    if (full) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<float4*>(dp + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+    } else {
+      for (int j = 0; j < 32 && col0 + j < p.N; ++j) dp[j] = v[j];
+    }
+  } else {
+    __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + d_off + static_cast<long long>(row) * p.ldd + col0;
+    if (full) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 o;
+        o.x = pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+        o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+        o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+        o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+        *reinterpret_cast<uint4*>(dp + 8 * q) = o;
+      }
+    } else {
+      for (int j = 0; j < 32 && col0 + j < p.N; ++j) dp[j] = __float2bfloat16(v[j]);
+    }
+  }
+}
+
+template <int CG, int BN, int A_MN, int B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Params p) {
+  using Cfg = Config<CG, BN>;
+  constexpr int STAGES = Cfg::STAGES;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;                                   // STAGES x A_BYTES
+  uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;           // STAGES x B_BYTES
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full_bar = bars;                  // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;        // [STAGES]
+  uint64_t* tmem_full = bars + 2 * STAGES;    // [2]
+  uint64_t* tmem_empty = bars + 2 * STAGES + 2;  // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const bool leader = (cta_rank == 0);
+  const int cluster_id = (CG == 2) ? (blockIdx.x >> 1) : blockIdx.x;
+  const int num_clusters = (CG == 2) ? (gridDim.x >> 1) : gridDim.x;
+  const int num_tiles = p.m_blocks * p.n_blocks * p.batch;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&map_a);
+    prefetch_tensormap(&map_b);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], NUM_EPI_WARPS * CG);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc<CG>(tmem_ptr, Cfg::TMEM_COLS);
+  }
+  tcgen05_fence_before();
+  if constexpr (CG == 2) {
+    cluster_sync();
+  } else {
+    __syncthreads();
+  }
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ============================ TMA producer ============================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        int bi, m_blk, n_blk;
+        tile_coords(p, tile, bi, m_blk, n_blk);
+        const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
+        const int m0 = (m_blk * CG + static_cast<int>(cta_rank)) * BM;
+        const int n0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
+          uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
+          const int k0 = kb * BK;
+          if (CG == 1 || leader) mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES * CG);
+          if constexpr (CG == 1) {
+            if constexpr (A_MN) {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j)
+                tma_load_4d(sa + j * 8192, &map_a, &full_bar[stage], m0 + 64 * j, k0, b_in, b_out);
+            } else {
+              tma_load_4d(sa, &map_a, &full_bar[stage], k0, m0, b_in, b_out);
+            }
+            if constexpr (B_MN) {
+#pragma unroll
+              for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
+                tma_load_4d(sb + j * 8192, &map_b, &full_bar[stage], n0 + 64 * j, k0, b_in, b_out);
+            } else {
+              tma_load_4d(sb, &map_b, &full_bar[stage], k0, n0, b_in, b_out);
+            }
+          } else {
+            if constexpr (A_MN) {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j)
+                tma_load_4d_2sm(sa + j * 8192, &map_a, &full_bar[stage], m0 + 64 * j, k0, b_in, b_out);
+            } else {
+              tma_load_4d_2sm(sa, &map_a, &full_bar[stage], k0, m0, b_in, b_out);
+            }
+            if constexpr (B_MN) {
+#pragma unroll
+              for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
+                tma_load_4d_2sm(sb + j * 8192, &map_b, &full_bar[stage], n0 + 64 * j, k0, b_in, b_out);
+            } else {
+              tma_load_4d_2sm(sb, &map_b, &full_bar[stage], k0, n0, b_in, b_out);
+            }
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================= MMA issuer =============================
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CG, BN, A_MN, B_MN);
+      // bytes to advance the descriptor start address per UMMA_K (16 elements of K):
+      //   K-major: 32 bytes inside the 128-byte swizzled row; MN-major: two 8-row groups of 128 B rows
+      constexpr uint32_t A_KSTEP = A_MN ? 2048u : 32u;
+      constexpr uint32_t B_KSTEP = B_MN ? 2048u : 32u;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tcgen05_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t da = umma_smem_desc(a_addr + k * A_KSTEP, p.lbo_a, p.sbo_a);
+            const uint64_t db = umma_smem_desc(b_addr + k * B_KSTEP, p.lbo_b, p.sbo_b);
+            umma_f16<CG>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          if constexpr (CG == 1) {
+            umma_commit(&empty_bar[stage]);
+          } else {
+            umma_commit_2sm(&empty_bar[stage], 0x3);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        if constexpr (CG == 1) {
+          umma_commit(&tmem_full[acc]);
+        } else {
+          umma_commit_2sm(&tmem_full[acc], 0x3);
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ============================== epilogue ==============================
+    const int quad = warp & 3;   // TMEM lane quadrant this warp may access
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int bi, m_blk, n_blk;
+      tile_coords(p, tile, bi, m_blk, n_blk);
+      const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
+      const long long d_off = b_in * p.d_si + b_out * p.d_so;
+      const long long aux_off = b_in * p.aux_si + b_out * p.aux_so;
+      const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BM + quad * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tcgen05_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t raw[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, raw);
+        tmem_ld_wait();
+        epilogue_chunk(p, raw, row, n0 + c * 32, d_off, aux_off);
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (CG == 1 || leader) {
+          mbar_arrive(&tmem_empty[acc]);
+        } else {
+          mbar_arrive_cluster(&tmem_empty[acc], 0);
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tcgen05_fence_before();
+  if constexpr (CG == 2) {
+    cluster_sync();
+  } else {
+    __syncthreads();
+  }
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc<CG>(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------
+static int make_operand_map(CUtensorMap* map, const void* base, int mn_major, int rows_mn, int k, long long ld,
+                            int batch_inner, int batch_outer, long long stride_inner, long long stride_outer,
+                            int box_mn_rows) {
+  // K-major: global [MN rows, K cols], box [box_mn_rows x 64];  MN-major: global [K rows, MN cols], box [64 x 64]
+  uint64_t dims[4];
+  uint32_t box[4];
+  if (mn_major) {
+    dims[0] = static_cast<uint64_t>(rows_mn);
+    dims[1] = static_cast<uint64_t>(k);
+    box[0] = 64;
+    box[1] = 64;
+  } else {
+    dims[0] = static_cast<uint64_t>(k);
+    dims[1] = static_cast<uint64_t>(rows_mn);
+    box[0] = 64;
+    box[1] = static_cast<uint32_t>(box_mn_rows);
+  }
+  dims[2] = static_cast<uint64_t>(batch_inner);
+  dims[3] = static_cast<uint64_t>(batch_outer);
+  box[2] = 1;
+  box[3] = 1;
+  const uint64_t row_bytes = static_cast<uint64_t>(ld) * 2;
+  uint64_t strides[3];
+  strides[0] = row_bytes;
+  strides[1] = batch_inner > 1 ? static_cast<uint64_t>(stride_inner) * 2 : row_bytes * dims[1];
+  strides[2] = batch_outer > 1 ? static_cast<uint64_t>(stride_outer) * 2 : strides[1] * dims[2];
+  return get_tensor_map_bf16(map, base, dims, strides, box);
+}
+
+template <int CG, int BN, int A_MN, int B_MN>
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t stream) {
+  using Cfg = Config<CG, BN>;
+  auto kernel = gemm_kernel<CG, BN, A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    DTB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DTB_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, ma, mb, p));
+  count_launch();
+  return 0;
+}
+
+template <int CG, int BN>
+static int dispatch_major(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int a_mn, int b_mn, int grid,
+                          cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch<CG, BN, 0, 0>(ma, mb, p, grid, s);
+  if (!a_mn && b_mn) return launch<CG, BN, 0, 1>(ma, mb, p, grid, s);
+  if (a_mn && !b_mn) return launch<CG, BN, 1, 0>(ma, mb, p, grid, s);
+  return launch<CG, BN, 1, 1>(ma, mb, p, grid, s);
+}
+
+}  // namespace gemm
+}  // namespace dtb
+
+extern "C" int dtb_gemm_bf16(const dtb_gemm_args* a, void* stream) {
+  using namespace dtb;
+  using namespace dtb::gemm;
+  DTB_REQUIRE(a != nullptr, "dtb_gemm_bf16: null args");
+  DTB_REQUIRE(a->m > 0 && a->n > 0 && a->k > 0, "dtb_gemm_bf16: empty problem %dx%dx%d", a->m, a->n, a->k);
+  DTB_REQUIRE(a->lda % 8 == 0 && a->ldb % 8 == 0, "dtb_gemm_bf16: lda/ldb must be multiples of 8 elements");
+  DTB_REQUIRE((reinterpret_cast<uintptr_t>(a->a) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->b) & 15) == 0,
+              "dtb_gemm_bf16: A/B must be 16-byte aligned");
+  DTB_REQUIRE(a->ldd % (a->d_fp32 ? 4 : 8) == 0 && (reinterpret_cast<uintptr_t>(a->d) & 15) == 0,
+              "dtb_gemm_bf16: D must be 16-byte aligned with a 16-byte-multiple pitch");
+  if (a->aux)
+    DTB_REQUIRE(a->ld_aux % (a->aux_fp32 ? 4 : 8) == 0 && (reinterpret_cast<uintptr_t>(a->aux) & 15) == 0,
+                "dtb_gemm_bf16: aux must be 16-byte aligned with a 16-byte-multiple pitch");
+  DTB_REQUIRE(a->act != 2 || a->aux != nullptr, "dtb_gemm_bf16: act=2 (gelu') needs aux");
+  const int bi = a->batch_inner > 0 ? a->batch_inner : 1;
+  const int bo = a->batch_outer > 0 ? a->batch_outer : 1;
+  const int sms = sm_count();
+
+  // tile selection: pair mode for big problems; 128-wide N tiles when 256 would leave SMs idle
+  int cg = a->cta_pair;
+  int bn = a->tile_n;
+  if (bn == 0) {
+    const long long tiles256 = 1LL * ((a->m + 127) / 128) * ((a->n + 255) / 256) * bi * bo;
+    bn = (a->n > 128 && tiles256 >= sms) ? 256 : 128;
+    if (a->n <= 128) bn = 128;
+  }
+  DTB_REQUIRE(bn == 128 || bn == 256, "dtb_gemm_bf16: tile_n must be 128 or 256");
+  if (cg == 0) {
+    const long long tiles_pair = 1LL * ((a->m + 255) / 256) * ((a->n + bn - 1) / bn) * bi * bo;
+    cg = (bn == 256 && a->m >= 256 && tiles_pair >= sms / 2) ? 2 : 1;
+  }
+  DTB_REQUIRE(cg == 1 || (cg == 2 && bn == 256), "dtb_gemm_bf16: cta_pair=2 requires tile_n=256");
+
+  Params p = {};
+  p.M = a->m; p.N = a->n; p.K = a->k;
+  p.batch_inner = bi; p.batch = bi * bo;
+  p.m_blocks = (a->m + BM * cg - 1) / (BM * cg);
+  p.n_blocks = (a->n + bn - 1) / bn;
+  p.group_m = cg == 2 ? 8 : 16;
+  p.d = a->d; p.d2 = a->d2; p.aux = a->aux; p.bias = a->bias;
+  p.ldd = a->ldd; p.ld_aux = a->ld_aux;
+  p.d_si = a->d_stride_inner; p.d_so = a->d_stride_outer;
+  p.aux_si = a->aux_stride_inner; p.aux_so = a->aux_stride_outer;
+  p.d_fp32 = a->d_fp32; p.aux_fp32 = a->aux_fp32; p.bias_fp32 = a->bias_fp32;
+  p.act = a->act;
+  p.alpha = a->alpha; p.beta = a->beta;
+  // canonical 128B-swizzle layouts (cute/atom/mma_traits_sm100.hpp):
+  //   K-major : 8-row groups 1024 B apart (SBO); LBO unused (1)
+  //   MN-major: 64-wide MN blocks 8192 B apart (LBO); 8-row K groups 1024 B apart (SBO)
+  p.lbo_a = a->dbg_lbo_a ? a->dbg_lbo_a : (a->a_mn_major ? 8192u : 16u);
+  p.sbo_a = a->dbg_sbo_a ? a->dbg_sbo_a : 1024u;
+  p.lbo_b = a->dbg_lbo_b ? a->dbg_lbo_b : (a->b_mn_major ? 8192u : 16u);
+  p.sbo_b = a->dbg_sbo_b ? a->dbg_sbo_b : 1024u;
+
+  CUtensorMap ma, mb;
+  if (make_operand_map(&ma, a->a, a->a_mn_major, a->m, a->k, a->lda, bi, bo, a->a_stride_inner, a->a_stride_outer, BM))
+    return 1;
+  if (make_operand_map(&mb, a->b, a->b_mn_major, a->n, a->k, a->ldb, bi, bo, a->b_stride_inner, a->b_stride_outer,
+                       bn / cg))
+    return 1;
+
+  const long long tiles = 1LL * p.m_blocks * p.n_blocks * p.batch;
+  int max_ctas = a->max_ctas > 0 ? (a->max_ctas < sms ? a->max_ctas : sms) : sms;
+  int grid;
+  if (cg == 2) {
+    long long clusters = max_ctas / 2;
+    if (clusters < 1) clusters = 1;
+    if (tiles < clusters) clusters = tiles;
+    grid = static_cast<int>(clusters * 2);
+  } else {
+    grid = static_cast<int>(tiles < max_ctas ? tiles : max_ctas);
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (cg == 2) return dispatch_major<2, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+  if (bn == 256) return dispatch_major<1, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+  return dispatch_major<1, 128>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+}

@@ -1,0 +1,270 @@
+// LayerNorm forward / backward for transformer rows (768, 1600, ... <= 4096 columns).
+// One warp owns one row: 16-byte loads, row held in registers, fp32 statistics via
+// shuffles.  Forward optionally fuses the residual add that precedes every LN in a
+// pre-LN GPT-2 block (y = LN(x + r), xres = x + r).  Backward produces dx (plus the
+// incoming residual-stream gradient) and accumulates dgamma/dbeta per CTA in shared
+// memory; CTA partials go to a caller-provided scratch buffer and a second kernel
+// reduces them in a fixed order (deterministic).
+//
+// Replaces ATen native_layer_norm(+backward) for the GPT-2 configs.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include "../../include/dtb200.h"
+#include "../common/host.h"
+
+namespace dtb {
+namespace ln {
+
+constexpr int WARPS = 4;
+constexpr int MAXV = 16;                 // 16 vectors x 8 elements x 32 lanes = 4096 columns
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& raw, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 raw;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return raw;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(WARPS * 32)
+fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+           const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
+           __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ xres, float* __restrict__ mean,
+           float* __restrict__ rstd, int rows, int cols, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = cols >> 3;
+  for (int row = blockIdx.x * WARPS + warp; row < rows; row += gridDim.x * WARPS) {
+    const long long base = static_cast<long long>(row) * cols;
+    float v[NV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) {
+        uint4 raw = *reinterpret_cast<const uint4*>(x + base + vi * 8);
+        unpack8(raw, v[i]);
+        if (res != nullptr) {
+          float r[8];
+          uint4 rr = *reinterpret_cast<const uint4*>(res + base + vi * 8);
+          unpack8(rr, r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[i][j] += r[j];
+          uint4 packed = pack8(v[i]);
+          *reinterpret_cast<uint4*>(xres + base + vi * 8) = packed;
+          unpack8(packed, v[i]);   // normalise exactly what backward will re-read
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[i][j];
+      }
+    }
+    const float mu = warp_sum(s) / cols;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      if (lane + 32 * i < nvec) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float d = v[i][j] - mu;
+          sq += d * d;
+        }
+      }
+    }
+    const float rs = rsqrtf(warp_sum(sq) / cols + eps);
+    if (lane == 0) {
+      mean[row] = mu;
+      rstd[row] = rs;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) {
+        float g[8], b[8], o[8];
+        unpack8(*reinterpret_cast<const uint4*>(gamma + vi * 8), g);
+        unpack8(*reinterpret_cast<const uint4*>(beta + vi * 8), b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mu) * rs * g[j] + b[j];
+        *reinterpret_cast<uint4*>(y + base + vi * 8) = pack8(o);
+      }
+    }
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(WARPS * 32)
+bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+              const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
+              const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx, int rows, int cols) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = cols >> 3;
+  for (int row = blockIdx.x * WARPS + warp; row < rows; row += gridDim.x * WARPS) {
+    const long long base = static_cast<long long>(row) * cols;
+    const float mu = mean[row], rs = rstd[row];
+    float xh[NV][8], wdy[NV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) {
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(gamma + vi * 8), g);
+        unpack8(*reinterpret_cast<const uint4*>(dy + base + vi * 8), wdy[i]);
+        unpack8(*reinterpret_cast<const uint4*>(x + base + vi * 8), xh[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xh[i][j] - mu) * rs;
+          wdy[i][j] *= g[j];
+          s1 += wdy[i][j];
+          s2 += wdy[i][j] * xh[i][j];
+        }
+      }
+    }
+    s1 = warp_sum(s1) / cols;
+    s2 = warp_sum(s2) / cols;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rs * (wdy[i][j] - s1 - xh[i][j] * s2);
+        if (dres != nullptr) {
+          float r[8];
+          unpack8(*reinterpret_cast<const uint4*>(dres + base + vi * 8), r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
+        }
+        *reinterpret_cast<uint4*>(dx + base + vi * 8) = pack8(o);
+      }
+    }
+  }
+}
+
+// dgamma/dbeta partial sums: CTA (bx, by) owns 64 columns and every PARAM_CHUNKS-th
+// block of rows; partial[by][0|1][cols].
+constexpr int PARAM_CHUNKS = 32;
+__global__ void __launch_bounds__(256)
+bwd_param_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                 const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ partial,
+                 int rows, int cols) {
+  __shared__ float pg[32][65];
+  __shared__ float pb[32][65];
+  const int cx = threadIdx.x & 7, ry = threadIdx.x >> 3;
+  const int col = blockIdx.x * 64 + cx * 8;
+  float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (col < cols) {
+    for (int r = blockIdx.y * 32 + ry; r < rows; r += gridDim.y * 32) {
+      float d[8], xv[8];
+      unpack8(*reinterpret_cast<const uint4*>(dy + static_cast<long long>(r) * cols + col), d);
+      unpack8(*reinterpret_cast<const uint4*>(x + static_cast<long long>(r) * cols + col), xv);
+      const float mu = mean[r], rs = rstd[r];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        ag[j] += d[j] * (xv[j] - mu) * rs;
+        ab[j] += d[j];
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    pg[ry][cx * 8 + j] = ag[j];
+    pb[ry][cx * 8 + j] = ab[j];
+  }
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int c = threadIdx.x & 63;
+    const bool is_beta = threadIdx.x >= 64;
+    float s = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) s += is_beta ? pb[r][c] : pg[r][c];
+    const int gc = blockIdx.x * 64 + c;
+    if (gc < cols) partial[(static_cast<long long>(blockIdx.y) * 2 + (is_beta ? 1 : 0)) * cols + gc] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bwd_finish_kernel(const float* __restrict__ partial, int nparts, int cols, float* __restrict__ dgamma,
+                  float* __restrict__ dbeta, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 2 * cols) return;
+  float s = 0.f;
+  for (int p = 0; p < nparts; ++p) s += partial[static_cast<long long>(p) * 2 * cols + c];
+  float* dst = c < cols ? dgamma + c : dbeta + (c - cols);
+  *dst = accumulate ? *dst + s : s;
+}
+
+}  // namespace ln
+}  // namespace dtb
+using namespace dtb;
+using namespace dtb::ln;
+
+extern "C" int dtb_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                                 void* xres_out, float* mean, float* rstd, int rows, int cols, float eps,
+                                 void* stream) {
+  DTB_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= MAXV * 256,
+              "dtb_layernorm_fwd: cols=%d must be a multiple of 8 and <= %d", cols, MAXV * 256);
+  DTB_REQUIRE(residual == nullptr || xres_out != nullptr, "dtb_layernorm_fwd: residual given without xres_out");
+  int grid = (rows + WARPS - 1) / WARPS;
+  const int cap = sm_count() * 16;
+  if (grid > cap) grid = cap;
+  auto s = static_cast<cudaStream_t>(stream);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto R = static_cast<const __nv_bfloat16*>(residual);
+  auto G = static_cast<const __nv_bfloat16*>(gamma);
+  auto B = static_cast<const __nv_bfloat16*>(beta);
+  auto Y = static_cast<__nv_bfloat16*>(y);
+  auto XR = static_cast<__nv_bfloat16*>(xres_out);
+  const int nv = (cols / 8 + 31) / 32;
+  if (nv <= 4) fwd_kernel<4><<<grid, WARPS * 32, 0, s>>>(X, R, G, B, Y, XR, mean, rstd, rows, cols, eps);
+  else if (nv <= 8) fwd_kernel<8><<<grid, WARPS * 32, 0, s>>>(X, R, G, B, Y, XR, mean, rstd, rows, cols, eps);
+  else fwd_kernel<MAXV><<<grid, WARPS * 32, 0, s>>>(X, R, G, B, Y, XR, mean, rstd, rows, cols, eps);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" size_t dtb_layernorm_bwd_scratch_floats(int rows, int cols) {
+  (void)rows;
+  return static_cast<size_t>(PARAM_CHUNKS) * 2 * static_cast<size_t>(cols);
+}
+
+extern "C" int dtb_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                                 const float* rstd, const void* dres_in, void* dx, float* dgamma, float* dbeta,
+                                 float* scratch, int rows, int cols, int accumulate_param_grads, void* stream) {
+  DTB_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 8 * 256,
+              "dtb_layernorm_bwd: cols=%d must be a multiple of 8 and <= 2048", cols);
+  DTB_REQUIRE(scratch != nullptr, "dtb_layernorm_bwd: scratch is required");
+  int grid = (rows + WARPS - 1) / WARPS;
+  const int cap = sm_count() * 8;
+  if (grid > cap) grid = cap;
+  auto s = static_cast<cudaStream_t>(stream);
+  const int nv = (cols / 8 + 31) / 32;
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto G = static_cast<const __nv_bfloat16*>(gamma);
+  auto DR = static_cast<const __nv_bfloat16*>(dres_in);
+  auto DX = static_cast<__nv_bfloat16*>(dx);
+  if (nv <= 4) bwd_dx_kernel<4><<<grid, WARPS * 32, 0, s>>>(DY, X, G, mean, rstd, DR, DX, rows, cols);
+  else bwd_dx_kernel<8><<<grid, WARPS * 32, 0, s>>>(DY, X, G, mean, rstd, DR, DX, rows, cols);
+  DTB_LAUNCH_OK();
+  bwd_param_kernel<<<dim3((cols + 63) / 64, PARAM_CHUNKS), 256, 0, s>>>(DY, X, mean, rstd, scratch, rows, cols);
+  DTB_LAUNCH_OK();
+  bwd_finish_kernel<<<(2 * cols + 255) / 256, 256, 0, s>>>(scratch, PARAM_CHUNKS, cols, dgamma, dbeta, accumulate_param_grads);
+  DTB_LAUNCH_OK();
+  return 0;
+}

@@ -1,0 +1,138 @@
+"""MLP family: the toy regression MLP (BASELINE.json config 1) and the wide
+8 x 8192 bf16 MLP (config 2).
+
+The reference's only model is ``torch.nn.Linear(20, 1)``
+(/root/reference/src/distributed_trainer.py:199); these are the north-star
+extensions of the same idea.  ``forward`` is ordinary autograd-visible PyTorch
+(CPU tests, arbitrary wrappers).  ``forward_backward`` is the B200 path: every
+Linear forward / dgrad / wgrad is one ``tcgen05`` GEMM with its bias, GELU or
+GELU' fused into the epilogue, the loss is a fused softmax-CE kernel, gradients
+are written straight into the caller's gradient buckets and the bucket is
+handed to the reducer the moment a layer's wgrad has been queued.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from ..ops import native
+
+
+class MLP(nn.Module):
+    """``num_layers`` Linear layers with tanh-GELU between them."""
+
+    supports_sharded_native = False
+
+    def __init__(self, input_size: int, hidden_size: int, output_size: int, num_layers: int = 2,
+                 dtype: torch.dtype = torch.float32, bias: bool = True) -> None:
+        super().__init__()
+        if num_layers < 1:
+            raise ValueError("num_layers must be >= 1")
+        dims = [input_size] + [hidden_size] * (num_layers - 1) + [output_size]
+        self.layers = nn.ModuleList(
+            [nn.Linear(dims[i], dims[i + 1], bias=bias, dtype=dtype) for i in range(num_layers)])
+        self.dims = dims
+        self._ws: Dict[Tuple[int, torch.device], Dict[str, Any]] = {}
+
+    def fsdp_units(self) -> List[nn.Module]:
+        return list(self.layers)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        h = x
+        last = len(self.layers) - 1
+        for i, layer in enumerate(self.layers):
+            h = layer(h)
+            if i != last:
+                h = F.gelu(h, approximate="tanh")
+        return h
+
+    # ------------------------------------------------------------------ native
+    def native_ready(self) -> bool:
+        """The tcgen05 path needs CUDA bf16 parameters and 8-element-aligned widths."""
+        p = self.layers[0].weight
+        return (p.is_cuda and p.dtype == torch.bfloat16 and native.available()
+                and all(d % 8 == 0 for d in self.dims))
+
+    def _workspace(self, rows: int, device: torch.device) -> Dict[str, Any]:
+        key = (rows, device)
+        ws = self._ws.get(key)
+        if ws is None:
+            bf = dict(dtype=torch.bfloat16, device=device)
+            n = len(self.layers)
+            ws = {
+                "z": [torch.empty(rows, self.dims[i + 1], **bf) for i in range(n - 1)],   # pre-activations
+                "h": [torch.empty(rows, self.dims[i + 1], **bf) for i in range(n - 1)],   # activations
+                "logits": torch.empty(rows, self.dims[-1], **bf),
+                "dz": [torch.empty(rows, max(self.dims[1:-1] or [8]), **bf) for _ in range(2)],
+                "row_loss": torch.empty(rows, dtype=torch.float32, device=device),
+                "loss": torch.empty((), dtype=torch.float32, device=device),
+            }
+            self._ws = {key: ws}      # one live batch shape at a time
+        return ws
+
+    def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, loss: str = "cross_entropy",
+                         grad_sink: Any = None, max_ctas: int = 0) -> torch.Tensor:
+        """Fused training step (no autograd).  Returns the mean loss (0-dim fp32 tensor).
+
+        ``grad_sink`` (a ``ReplicatedModule``) supplies ``grad_view(param)`` and
+        ``mark_ready(param)``; without one, gradients land in ``param.grad``.
+        """
+        if loss != "cross_entropy" or targets.dtype != torch.int64:
+            raise NotImplementedError("native MLP step supports cross_entropy with int64 class targets")
+        x = inputs.contiguous()
+        rows = x.shape[0]
+        ws = self._workspace(rows, x.device)
+        n = len(self.layers)
+
+        def grad_of(p: nn.Parameter) -> torch.Tensor:
+            if grad_sink is not None:
+                return grad_sink.grad_view(p)
+            if p.grad is None:
+                p.grad = torch.empty_like(p)
+            return p.grad
+
+        # ---- forward: h_{i+1} = gelu(h_i W_i^T + b_i), pre-activation kept for backward
+        h = x
+        for i, layer in enumerate(self.layers):
+            out_f, in_f = layer.weight.shape
+            if i != n - 1:
+                native.gemm(h, layer.weight, ws["h"][i], m=rows, n=out_f, k=in_f, bias=layer.bias, act=1,
+                            d2=ws["z"][i], max_ctas=max_ctas)
+                h = ws["h"][i]
+            else:
+                native.gemm(h, layer.weight, ws["logits"], m=rows, n=out_f, k=in_f, bias=layer.bias,
+                            max_ctas=max_ctas)
+        # ---- loss + dlogits in place
+        native.cross_entropy_fwd_bwd(ws["logits"], targets, ws["row_loss"], self.dims[-1], 1.0 / rows)
+        native.mean_f32(ws["row_loss"], ws["loss"])
+        # ---- backward, last layer first; each layer's grads go to the reducer as soon as queued
+        dz = ws["logits"]
+        for i in range(n - 1, -1, -1):
+            layer = self.layers[i]
+            out_f, in_f = layer.weight.shape
+            h_in = x if i == 0 else ws["h"][i - 1]
+            # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major)
+            native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
+                        lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
+            if layer.bias is not None:
+                native.colsum(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
+            if grad_sink is not None:
+                grad_sink.mark_ready(layer.weight)
+                if layer.bias is not None:
+                    grad_sink.mark_ready(layer.bias)
+            if i > 0:
+                # dgrad fused with GELU': dz_prev = (dz W_i) * gelu'(z_{i-1})
+                nxt = ws["dz"][i % 2]
+                native.gemm(dz, layer.weight, nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
+                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=max_ctas)
+                dz = nxt
+        return ws["loss"]
+
+
+def wide_mlp(dtype: torch.dtype = torch.bfloat16, width: int = 8192, depth: int = 8) -> MLP:
+    """BASELINE.json config 2."""
+    return MLP(width, width, width, depth, dtype=dtype)

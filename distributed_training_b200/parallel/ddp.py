@@ -1,0 +1,292 @@
+"""Hand-rolled replicated data parallelism.
+
+What the reference gets from ``torch.nn.parallel.DistributedDataParallel``
+(/root/reference/src/dist_strategy/ddp_strategy.py:18) and what its playground
+spells out by hand (/root/reference/src/playground/ddp_script.py:120-121,149-154)
+is implemented here directly:
+
+* at wrap time rank 0's parameters and buffers are broadcast to every rank;
+* gradients live in flat *buckets* (reverse registration order, 1 MiB first
+  bucket, ``bucket_cap_mb`` afterwards); each ``param.grad`` is a view into
+  its bucket, so reduced values are visible to the optimizer without a copy;
+* a post-accumulate-grad hook per parameter counts the bucket down and
+  launches its all-reduce the moment the last gradient lands, so
+  communication overlaps the rest of backward; averaging (and, on B200, the
+  bf16/fp32 cast) happens inside the collective;
+* an autograd-engine callback joins all in-flight buckets at the end of
+  backward, so ``loss.backward(); optimizer.step()`` works unchanged.
+
+Models that implement ``forward_backward(inputs, targets, grad_sink=...)``
+(the native MLP / GPT-2) bypass autograd: their wgrad kernels write straight
+into the bucket views and call :meth:`ReplicatedModule.mark_ready`.
+
+The wrapper is communicator-agnostic: gloo on CPU (``TorchDistComm``), the
+peer-memory kernels on B200 (``SymmComm``).
+"""
+from __future__ import annotations
+
+import contextlib
+import logging
+import time
+from typing import Any, Dict, Iterator, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from .buckets import BucketPlan, plan_buckets
+from .comm import Communicator, Work, make_communicator
+from .strategy import DistributedStrategy, OptimizerSpec, atomic_torch_save
+
+logger = logging.getLogger(__name__)
+
+
+class GradBucket:
+    """Flat gradient buffer plus the bookkeeping for one reduction per step."""
+
+    def __init__(self, plan: BucketPlan, buffer: torch.Tensor, params: List[nn.Parameter]) -> None:
+        self.plan = plan
+        self.buffer = buffer
+        self.views: Dict[int, torch.Tensor] = {}
+        for slot in plan.slots:
+            self.views[slot.param_index] = buffer[slot.offset: slot.offset + slot.numel].view(slot.shape)
+        self.expected = len(plan.slots)
+        self.pending = self.expected
+        self.ready: set = set()
+        self.work: Optional[Work] = None
+        self.launched = False
+
+    def reset(self) -> None:
+        self.pending = self.expected
+        self.ready.clear()
+        self.work = None
+        self.launched = False
+
+
+class ReplicatedModule(nn.Module):
+    """``module`` replicated on every rank with bucketed, overlapped gradient averaging.
+
+    ``state_dict()`` keys carry the ``module.`` prefix, exactly like torch's
+    DDP wrapper, so snapshots are interchangeable with the reference's
+    (SURVEY §5.4).
+    """
+
+    def __init__(self, module: nn.Module, comm: Communicator, bucket_cap_mb: float = 25.0,
+                 first_bucket_mb: float = 1.0, init_sync: bool = True,
+                 grad_dtype: Optional[torch.dtype] = None) -> None:
+        super().__init__()
+        self.module = module
+        self.comm = comm
+        self.require_backward_grad_sync = True
+        self._params: List[nn.Parameter] = [p for p in module.parameters() if p.requires_grad]
+        self._index_of: Dict[int, int] = {id(p): i for i, p in enumerate(self._params)}
+        if init_sync:
+            self.sync_parameters()
+
+        plans = plan_buckets(self._params, int(bucket_cap_mb * (1 << 20)),
+                             int(first_bucket_mb * (1 << 20)), reverse=True, grad_dtype=grad_dtype)
+        comm.reserve(sum(pl.nbytes + 256 for pl in plans))
+        self.buckets: List[GradBucket] = []
+        self._bucket_of: Dict[int, GradBucket] = {}
+        for plan in plans:
+            bucket = GradBucket(plan, comm.alloc(plan.numel, plan.dtype), self._params)
+            self.buckets.append(bucket)
+            for idx in plan.param_indices:
+                self._bucket_of[idx] = bucket
+        self._hook_handles = []
+        for i, p in enumerate(self._params):
+            self._hook_handles.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+        self.attach_grad_views()
+        self._callback_queued = False
+        self._in_manual_step = False
+        #: seconds (CPU) or milliseconds of stream stall (CUDA) the last step spent
+        #: waiting for gradient communication after backward had finished
+        self.last_exposed_comm_ms = 0.0
+        self._stall_events: Optional[Tuple[Any, Any]] = None
+
+    # ------------------------------------------------------------------ setup
+    def sync_parameters(self, src: int = 0) -> None:
+        """Broadcast rank ``src``'s parameters and buffers (DDP init sync)."""
+        tensors = [p.data for p in self.module.parameters()] + [b.data for b in self.module.buffers()]
+        self.comm.broadcast_(tensors, src=src)
+
+    def attach_grad_views(self) -> None:
+        """Point every ``param.grad`` at its bucket view (zero-filled)."""
+        for i, p in enumerate(self._params):
+            view = self._bucket_of[i].views[i]
+            if p.grad is not None and p.grad.data_ptr() != view.data_ptr():
+                view.copy_(p.grad)
+            p.grad = view if view.dtype == p.dtype else None
+
+    def forward(self, *args: Any, **kwargs: Any) -> Any:
+        return self.module(*args, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self) -> Iterator[None]:
+        """Skip gradient averaging inside the context (gradient accumulation)."""
+        previous = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = previous
+
+    # ------------------------------------------------------------ autograd path
+    def _make_hook(self, index: int):
+        def hook(param: torch.Tensor) -> None:
+            if not self.require_backward_grad_sync or self._in_manual_step:
+                return
+            bucket = self._bucket_of[index]
+            view = bucket.views[index]
+            grad = param.grad
+            if grad is not None and grad.data_ptr() != view.data_ptr():
+                # optimizer.zero_grad(set_to_none=True) detached the view: land the fresh
+                # gradient in the bucket and re-attach so the optimizer reads the reduced value
+                view.copy_(grad)
+                if view.dtype == param.dtype:
+                    param.grad = view
+            if not self._callback_queued:
+                self._callback_queued = True
+                torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+            self._count_down(bucket, index)
+
+        return hook
+
+    def _count_down(self, bucket: GradBucket, index: int) -> None:
+        if index in bucket.ready:
+            return
+        bucket.ready.add(index)
+        bucket.pending -= 1
+        if bucket.pending == 0:
+            self._launch(bucket)
+
+    def _launch(self, bucket: GradBucket) -> None:
+        bucket.work = self.comm.all_reduce_avg_(bucket.buffer)
+        bucket.launched = True
+
+    def _finalize_backward(self) -> None:
+        self._callback_queued = False
+        self.finish_gradient_sync()
+
+    # --------------------------------------------------------------- manual path
+    def grad_view(self, param: nn.Parameter) -> torch.Tensor:
+        """Bucket slice a native wgrad kernel should write ``param``'s gradient into."""
+        i = self._index_of[id(param)]
+        return self._bucket_of[i].views[i]
+
+    def mark_ready(self, param: nn.Parameter) -> None:
+        """Declare ``param``'s gradient final for this step (native models call this)."""
+        if not self.require_backward_grad_sync:
+            return
+        i = self._index_of[id(param)]
+        self._count_down(self._bucket_of[i], i)
+
+    def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, **kwargs: Any) -> torch.Tensor:
+        """One fused forward+backward of a native model with overlapped reduction."""
+        if not hasattr(self.module, "forward_backward"):
+            raise AttributeError(f"{type(self.module).__name__} has no native forward_backward")
+        self._in_manual_step = True
+        try:
+            loss = self.module.forward_backward(inputs, targets, grad_sink=self, **kwargs)
+        finally:
+            self._in_manual_step = False
+        self.finish_gradient_sync()
+        return loss
+
+    def finish_gradient_sync(self) -> None:
+        """Join every bucket; unused parameters contribute zeros."""
+        if not self.require_backward_grad_sync:
+            return
+        for bucket in self.buckets:
+            if not bucket.launched:
+                for idx, view in bucket.views.items():
+                    if idx not in bucket.ready:
+                        view.zero_()
+                self._launch(bucket)
+        cuda = self.comm.device.type == "cuda"
+        if cuda:
+            start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            start.record()
+        t0 = time.perf_counter()
+        for bucket in self.buckets:
+            if bucket.work is not None:
+                bucket.work.wait()
+        if cuda:
+            stop.record()
+            self._stall_events = (start, stop)
+        else:
+            self.last_exposed_comm_ms = (time.perf_counter() - t0) * 1e3
+        for i, p in enumerate(self._params):
+            view = self._bucket_of[i].views[i]
+            if view.dtype != p.dtype:            # reduced in a narrower wire dtype
+                if p.grad is None:
+                    p.grad = view.to(p.dtype)
+                else:
+                    p.grad.copy_(view)
+            elif p.grad is None:
+                p.grad = view
+        for bucket in self.buckets:
+            bucket.reset()
+
+    def exposed_comm_ms(self) -> float:
+        """Time the compute stream stalled on gradient communication last step."""
+        if self._stall_events is not None:
+            start, stop = self._stall_events
+            stop.synchronize()
+            self.last_exposed_comm_ms = start.elapsed_time(stop)
+            self._stall_events = None
+        return self.last_exposed_comm_ms
+
+    @property
+    def native_step(self) -> bool:
+        """True when the wrapped model runs its own fused forward+backward (no autograd)."""
+        return hasattr(self.module, "forward_backward") and getattr(self.module, "native_ready", lambda: False)()
+
+    def extra_repr(self) -> str:
+        sizes = ", ".join(f"{b.plan.nbytes / 2**20:.1f}MiB" for b in self.buckets)
+        return f"world={self.comm.world_size}, buckets=[{sizes}]"
+
+
+class DDPStrategy(DistributedStrategy):
+    """Replicated strategy; constructor signature as the reference's
+    ``DDPStrategy(local_rank, is_gpu)`` (/root/reference/src/dist_strategy/ddp_strategy.py:10-13)."""
+
+    def __init__(self, local_rank: int = 0, is_gpu: bool = False, bucket_cap_mb: float = 25.0,
+                 comm: Optional[Communicator] = None) -> None:
+        self.local_rank = local_rank
+        self.is_gpu = is_gpu
+        self.bucket_cap_mb = bucket_cap_mb
+        self.comm = comm
+
+    def _device(self, device: Any) -> torch.device:
+        if self.is_gpu:
+            return torch.device("cuda", self.local_rank if not isinstance(device, torch.device) or device.index is None
+                                else device.index)
+        return torch.device("cpu")
+
+    def prepare_model(self, model: nn.Module, device: Any) -> nn.Module:
+        if self.comm is None:
+            self.comm = make_communicator(self._device(device))
+        return ReplicatedModule(model, self.comm, bucket_cap_mb=self.bucket_cap_mb)
+
+    def save_checkpoint(self, model: nn.Module, state_dict: dict, path: str) -> None:
+        atomic_torch_save(state_dict, path)
+
+    def load_checkpoint(self, model: nn.Module, checkpoint: dict, device: Any) -> Tuple[nn.Module, int]:
+        state = checkpoint["MODEL_STATE"]
+        wrapped = isinstance(model, ReplicatedModule)
+        has_prefix = all(k.startswith("module.") for k in state) and len(state) > 0
+        if wrapped and not has_prefix:      # snapshot from the sharded strategy / a bare model
+            state = {f"module.{k}": v for k, v in state.items()}
+        elif not wrapped and has_prefix:
+            state = {k[len("module."):]: v for k, v in state.items()}
+        model.load_state_dict(state)
+        return model, int(checkpoint["EPOCHS_RUN"])
+
+    def build_optimizer(self, model: nn.Module, spec: OptimizerSpec) -> Any:
+        from ..optim import build_fused_optimizer
+
+        return build_fused_optimizer([p for p in model.parameters() if p.requires_grad], spec)
+
+    def barrier(self) -> None:
+        if self.comm is not None:
+            self.comm.barrier()

@@ -1,0 +1,266 @@
+"""Symmetric-memory communicator for B200 (NVLink 5 / NVSwitch peer access).
+
+Every rank allocates identically sized *segments* of device memory, exports
+them through CUDA IPC and maps all peers' segments, so rank ``r``'s buffer at
+``(segment, offset)`` has a known address in every process.  Collectives are
+single kernels from ``csrc/comm/collectives.cu`` that read and write those
+peer addresses directly; ``torch.distributed`` (gloo) is used only to exchange
+the 64-byte IPC handles and for host-side scalars.
+
+Replaces ``ProcessGroupNCCL`` as used by the reference
+(/root/reference/src/distributed_trainer.py:61-62).
+
+Buffers handed out by :meth:`SymmComm.alloc` are ordinary torch tensors backed
+by segment memory (via ``__cuda_array_interface__``), so gradient buckets and
+parameter shards can live in them with no staging copies.  Allocation is a
+deterministic bump allocator: every rank must call ``alloc`` with the same
+sizes in the same order (true for replicas of one model).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import os
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native
+from .comm import Communicator, Work
+
+logger = logging.getLogger(__name__)
+
+ALIGN = 256
+DEFAULT_SEGMENT_BYTES = int(os.environ.get("DTB200_SEGMENT_MB", "1024")) << 20
+
+
+class _RawBuffer:
+    """Exposes a raw device range to torch through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, nbytes: int, owner: object) -> None:
+        self._owner = owner
+        self.__cuda_array_interface__ = {
+            "shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2, "strides": None,
+        }
+
+
+@dataclass
+class Segment:
+    index: int
+    nbytes: int
+    local_ptr: int
+    peer_ptrs: List[int]
+    signal_ptrs: List[int]
+    desc: native.CommDesc
+    used: int = 0
+    base_tensor: Optional[torch.Tensor] = None
+
+
+class _StreamWork(Work):
+    """Completion = an event on the communication stream; ``wait`` orders the caller's stream after it."""
+
+    def __init__(self, event: "torch.cuda.Event") -> None:
+        self.event = event
+
+    def wait(self) -> None:
+        torch.cuda.current_stream().wait_event(self.event)
+
+
+class SymmComm(Communicator):
+    """Peer-memory communicator; one per process (one process per GPU)."""
+
+    def __init__(self, device: torch.device, segment_bytes: int = DEFAULT_SEGMENT_BYTES,
+                 comm_ctas: int = 0, overlap_stream: bool = True) -> None:
+        native.require()
+        self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        torch.cuda.set_device(self.device)
+        if dist.is_available() and dist.is_initialized():
+            self.rank, self.world_size = dist.get_rank(), dist.get_world_size()
+        else:
+            self.rank, self.world_size = 0, 1
+        if self.world_size not in (1, 2, 4, 8):
+            raise ValueError(f"SymmComm supports 1, 2, 4 or 8 ranks per node, got {self.world_size}")
+        self.segment_bytes = int(segment_bytes)
+        self.comm_ctas = comm_ctas
+        self.segments: List[Segment] = []
+        self._owner_of: Dict[int, Tuple[Segment, int]] = {}   # storage data_ptr -> (segment, offset)
+        self.stream = torch.cuda.Stream(self.device, priority=-1) if overlap_stream else None
+        self._closed = False
+        self._scratch: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------------ heap
+    def _exchange(self, payload: bytes) -> List[bytes]:
+        if self.world_size == 1:
+            return [payload]
+        gathered: List[Optional[bytes]] = [None] * self.world_size
+        dist.all_gather_object(gathered, payload)
+        return [g for g in gathered]  # type: ignore[misc]
+
+    def _new_segment(self, min_bytes: int) -> Segment:
+        nbytes = max(self.segment_bytes, (min_bytes + ALIGN - 1) // ALIGN * ALIGN)
+        total = nbytes + native.SIGNAL_PAD_BYTES
+        ptr, handle = native.symm_alloc(total)       # zero-filled, synchronised
+        handles = self._exchange(handle)
+        peer_ptrs = []
+        for r, h in enumerate(handles):
+            peer_ptrs.append(ptr if r == self.rank else native.symm_open(h))
+        desc = native.CommDesc()
+        for r in range(self.world_size):
+            desc.peers[r] = peer_ptrs[r]
+            desc.signals[r] = peer_ptrs[r] + nbytes
+        desc.mc_base = None
+        desc.rank, desc.world, desc.timeout_cycles = self.rank, self.world_size, 0
+        seg = Segment(len(self.segments), nbytes, ptr, peer_ptrs, [p + nbytes for p in peer_ptrs], desc)
+        seg.base_tensor = torch.as_tensor(_RawBuffer(ptr, nbytes, seg), device=self.device)
+        self.segments.append(seg)
+        if self.world_size > 1:
+            dist.barrier()     # every rank has mapped every peer before the first kernel touches it
+        logger.info(f"[rank {self.rank}] symmetric segment {seg.index}: {nbytes / 2**20:.0f} MiB mapped on "
+                    f"{self.world_size} ranks")
+        return seg
+
+    def reserve(self, nbytes: int) -> None:
+        """Make sure one segment has ``nbytes`` free, so buffers allocated next share a segment."""
+        nbytes = (nbytes + ALIGN - 1) // ALIGN * ALIGN
+        if not any(s.nbytes - s.used >= nbytes for s in self.segments):
+            self._new_segment(nbytes)
+
+    def alloc(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        esize = torch.empty((), dtype=dtype).element_size()
+        nbytes = (numel * esize + ALIGN - 1) // ALIGN * ALIGN
+        seg = next((s for s in self.segments if s.nbytes - s.used >= nbytes), None)
+        if seg is None:
+            seg = self._new_segment(nbytes)
+        offset = seg.used
+        seg.used += nbytes
+        flat = seg.base_tensor[offset: offset + nbytes].view(dtype)[:numel]  # type: ignore[index]
+        self._owner_of[flat.data_ptr()] = (seg, offset)
+        return flat
+
+    def locate(self, t: torch.Tensor) -> Tuple[Segment, int]:
+        """(segment, byte offset) of a tensor that lives in the symmetric heap."""
+        ptr = t.data_ptr()
+        hit = self._owner_of.get(ptr)
+        if hit is not None:
+            return hit
+        for seg in self.segments:
+            if seg.local_ptr <= ptr < seg.local_ptr + seg.nbytes:
+                return seg, ptr - seg.local_ptr
+        raise ValueError("tensor is not in the symmetric heap (allocate it with SymmComm.alloc)")
+
+    def in_heap(self, t: torch.Tensor) -> bool:
+        ptr = t.data_ptr()
+        return any(seg.local_ptr <= ptr < seg.local_ptr + seg.nbytes for seg in self.segments)
+
+    def scratch(self, nbytes: int) -> torch.Tensor:
+        """A reusable heap buffer for operands that were not allocated in the heap."""
+        if self._scratch is None or self._scratch.numel() < nbytes:
+            self._scratch = self.alloc(max(nbytes, 64 << 20), torch.uint8)
+        return self._scratch[:nbytes]
+
+    # ------------------------------------------------------------ collectives
+    def _on_comm_stream(self):
+        """Order the comm stream after the caller's current stream and switch to it."""
+        if self.stream is None:
+            return torch.cuda.stream(torch.cuda.current_stream())
+        self.stream.wait_stream(torch.cuda.current_stream())
+        return torch.cuda.stream(self.stream)
+
+    def broadcast_(self, tensors: Sequence[torch.Tensor], src: int = 0) -> None:
+        if self.world_size == 1:
+            return
+        # coalesce into heap slabs, one peer-store kernel per slab
+        slab_cap = 256 << 20
+        group: List[torch.Tensor] = []
+        size = 0
+
+        def flush() -> None:
+            nonlocal group, size
+            if not group:
+                return
+            stage = self.scratch((size + 15) // 16 * 16)
+            seg, off = self.locate(stage)
+            cursor = 0
+            views = []
+            for t in group:
+                nb = t.numel() * t.element_size()
+                view = stage[cursor: cursor + nb].view(t.dtype).view(t.shape)
+                if self.rank == src:
+                    view.copy_(t)
+                views.append((t, view))
+                cursor += (nb + 15) // 16 * 16
+            native.comm_broadcast(seg.desc, off, (cursor + 15) // 16 * 16, src, self.comm_ctas)
+            if self.rank != src:
+                with torch.no_grad():
+                    for t, view in views:
+                        t.copy_(view)
+            group, size = [], 0
+
+        for t in tensors:
+            nb = (t.numel() * t.element_size() + 15) // 16 * 16
+            if size + nb > slab_cap:
+                flush()
+            group.append(t)
+            size += nb
+        flush()
+        torch.cuda.current_stream().synchronize()
+
+    def all_reduce_avg_(self, buf: torch.Tensor) -> Work:
+        if buf.dtype not in (torch.bfloat16, torch.float32):
+            raise TypeError(f"all_reduce_avg_ supports bf16/fp32, got {buf.dtype}")
+        seg, off = self.locate(buf)
+        esize = buf.element_size()
+        numel = (buf.numel() * esize + 15) // 16 * 16 // esize      # heap slots are padded to 256 B
+        with self._on_comm_stream():
+            native.comm_all_reduce_avg(seg.desc, off, numel, buf.dtype == torch.float32, 0, self.comm_ctas)
+            event = torch.cuda.Event()
+            event.record()
+        return _StreamWork(event)
+
+    def all_gather_into(self, out: torch.Tensor, shard: torch.Tensor) -> None:
+        seg_o, off_o = self.locate(out)
+        seg_s, off_s = self.locate(shard)
+        if seg_o is not seg_s:
+            raise ValueError("all_gather_into: out and shard must live in the same symmetric segment")
+        native.comm_all_gather(seg_o.desc, off_o, off_s, shard.numel(), shard.element_size(), self.comm_ctas)
+
+    def reduce_scatter_avg_into(self, out: torch.Tensor, full: torch.Tensor) -> None:
+        seg, off = self.locate(full)
+        native.comm_reduce_scatter_avg(seg.desc, out, off, out.numel(), full.dtype == torch.float32, self.comm_ctas)
+
+    def barrier(self) -> None:
+        if self.world_size == 1 or not self.segments:
+            if self.world_size > 1:
+                dist.barrier()
+            return
+        native.comm_barrier(self.segments[0].desc, 15)
+        torch.cuda.current_stream().synchronize()
+
+    def check_errors(self) -> None:
+        for seg in self.segments:
+            flag = native.comm_error_flag(seg.desc)
+            if flag:
+                raise RuntimeError(f"collective watchdog fired on rank {self.rank}: peer {flag - 1} never arrived")
+
+    def close(self) -> None:
+        if self._closed:
+            return
+        self._closed = True
+        try:
+            torch.cuda.synchronize(self.device)
+            if self.world_size > 1 and dist.is_initialized():
+                dist.barrier()
+        except Exception:  # pragma: no cover
+            pass
+        for seg in self.segments:
+            for r, p in enumerate(seg.peer_ptrs):
+                if r != self.rank:
+                    try:
+                        native.symm_close(p)
+                    except Exception:  # pragma: no cover
+                        pass
+        # the local allocations are released at process exit: live tensors may still point into them

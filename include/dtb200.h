@@ -1,0 +1,194 @@
+/*
+ * dtb200 — C ABI of the B200 (sm_100a) kernel library behind
+ * distributed_training_b200.  Every entry point:
+ *   - takes raw device pointers and a cudaStream_t passed as void*;
+ *   - is asynchronous with respect to the host unless stated otherwise;
+ *   - returns 0 on success, non-zero on failure (dtb_last_error() has the text);
+ *   - allocates no device memory unless its comment says so.
+ *
+ * Where a function replaces something the reference executes implicitly through
+ * PyTorch, the comment cites the reference call site (SURVEY.md §2.5 numbering).
+ */
+#ifndef DTB200_H_
+#define DTB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ------------------------------------------------------------ */
+const char* dtb_last_error(void);
+int dtb_version(void);
+/* Kernel launches issued by this library since load / the last reset (bench.py's gpu_launches). */
+long long dtb_launch_count(void);
+void dtb_reset_launch_count(void);
+
+/* ---- GEMM (K9/K10: nn.Linear forward, dgrad, wgrad → cuBLAS in the reference,
+ *      /root/reference/src/distributed_trainer.py:162,164) ----------------------
+ * D[m,n] = epilogue( alpha * sum_k A(m,k) * B(n,k) )   bf16 inputs, fp32 accumulation in TMEM.
+ *   a_mn_major = 0: A stored [M,K] row-major (pitch lda);  1: stored [K,M] row-major.
+ *   b_mn_major = 0: B stored [N,K] row-major (pitch ldb);  1: stored [K,N] row-major.
+ * Linear forward  Y = X W^T           : A = X  (K-major), B = W  (K-major)
+ * Linear dgrad    dX = dY W           : A = dY (K-major), B = W  (MN-major)
+ * Linear wgrad    dW = dY^T X         : A = dY (MN-major), B = X (MN-major)
+ * Epilogue, in order:  v = alpha*acc; v += bias[n]; act==1: (d2 = v if d2) v = gelu_tanh(v);
+ *   act==2: v *= gelu_tanh'(aux[m,n]);  otherwise if aux: v += beta*aux[m,n];  D = v.
+ * Batched over batch_outer x batch_inner problems with independent element strides
+ * (attention heads: inner = head, outer = batch).  All pitches/strides in elements;
+ * pitches must be multiples of 8 elements, base pointers 16-byte aligned. */
+typedef struct dtb_gemm_args {
+  const void* a; const void* b; void* d;
+  void* d2;              /* optional second output (pre-activation), same layout as d, bf16 */
+  const void* aux;       /* optional [M,N] operand (residual / pre-activation / accumulate-into) */
+  const void* bias;      /* optional [N] */
+  long long lda, ldb, ldd, ld_aux;
+  long long a_stride_inner, a_stride_outer;
+  long long b_stride_inner, b_stride_outer;
+  long long d_stride_inner, d_stride_outer;
+  long long aux_stride_inner, aux_stride_outer;
+  int m, n, k;
+  int batch_inner, batch_outer;
+  int a_mn_major, b_mn_major;
+  int d_fp32, aux_fp32, bias_fp32;
+  int act;               /* 0 none, 1 gelu(tanh), 2 multiply by gelu'(aux) */
+  float alpha, beta;
+  int tile_n;            /* 0 = auto, else 128 or 256 */
+  int cta_pair;          /* 0 = auto, 1 = force 1-CTA MMA, 2 = force cta_group::2 */
+  int max_ctas;          /* 0 = all SMs; otherwise cap the persistent grid (leave SMs to a comm kernel) */
+  unsigned dbg_lbo_a, dbg_sbo_a, dbg_lbo_b, dbg_sbo_b;   /* 0 = default; bring-up overrides */
+} dtb_gemm_args;
+int dtb_gemm_bf16(const dtb_gemm_args* args, void* stream);
+
+/* Tiny-shape Linear for the reference's own model sizes (K=20,N=1; K=10,N=1): fp32 SIMT kernels. */
+int dtb_linear_small_fwd(const float* x, const float* w, const float* b, float* y, int rows, int in_f, int out_f,
+                         void* stream);
+int dtb_linear_small_bwd(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db, int rows,
+                         int in_f, int out_f, void* stream);
+
+/* ---- elementwise / reductions -------------------------------------------- */
+int dtb_gelu_fwd_bf16(const void* x, void* y, long long n, void* stream);
+int dtb_gelu_bwd_bf16(const void* x, const void* dy, void* dx, long long n, void* stream);
+/* out[n] = sum_m x[m,n]  (bias gradient). bf16 in, out bf16 or fp32. Uses no scratch. */
+int dtb_colsum_bf16(const void* x, void* out, int rows, int cols, long long ldx, int out_fp32, void* stream);
+int dtb_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
+int dtb_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
+int dtb_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
+/* sum of squares of n elements into *out (fp32, accumulated with atomicAdd; caller zeroes). K15. */
+int dtb_sumsq(const void* x, int is_fp32, long long n, float* out, void* stream);
+
+/* ---- LayerNorm (K16) ------------------------------------------------------- */
+/* y = LN(x [+ residual]) * gamma + beta; when residual != NULL, xres_out receives x + residual. */
+int dtb_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                      void* xres_out, float* mean, float* rstd, int rows, int cols, float eps, void* stream);
+/* dx = LN backward (+ dres_in if given).  dgamma/dbeta are fp32 [cols]; partial sums go through
+ * `scratch` (fp32, at least dtb_layernorm_bwd_scratch_floats(rows, cols) floats). */
+size_t dtb_layernorm_bwd_scratch_floats(int rows, int cols);
+int dtb_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                      const void* dres_in, void* dx, float* dgamma, float* dbeta, float* scratch, int rows, int cols,
+                      int accumulate_param_grads, void* stream);
+
+/* ---- losses (K11/K12: F.cross_entropy / nn.MSELoss,
+ *      /root/reference/src/distributed_trainer.py:163, playground/ddp_script.py:135) */
+/* Fused softmax cross-entropy with index targets: per-row loss (fp32) and, in place over
+ * `logits`, dlogits = (softmax - onehot) * grad_scale.  Columns >= vocab (padding) get 0. */
+int dtb_cross_entropy_fwd_bwd(void* logits, const long long* targets, float* row_loss, int rows, int vocab,
+                              long long ld, float grad_scale, int write_grad, void* stream);
+/* Soft-target form the reference's trainer actually exercises (float targets, same shape). */
+int dtb_soft_cross_entropy_fwd_bwd(const float* logits, const float* targets, float* row_loss, float* dlogits,
+                                   int rows, int cols, float grad_scale, void* stream);
+int dtb_mse_fwd_bwd(const float* pred, const float* target, float* loss_sum, float* dpred, long long n,
+                    float grad_scale, void* stream);
+/* mean of n floats into *out */
+int dtb_mean_f32(const float* x, long long n, float* out, void* stream);
+
+/* ---- embedding (K16) -------------------------------------------------------- */
+int dtb_embedding_fwd(const long long* tokens, const void* wte, const void* wpe, void* out, int batch, int seq,
+                      int channels, void* stream);
+/* dwte[token] += dout (bf16x2 atomics), dwpe[t] = sum_b dout[b,t] */
+int dtb_embedding_bwd(const void* dout, const long long* tokens, void* dwte, void* dwpe, int batch, int seq,
+                      int channels, int accumulate_wte, void* stream);
+
+/* ---- attention (K16) ----------------------------------------------------------
+ * Causal self-attention over a packed qkv activation [batch, seq, 3*heads*64] (bf16).
+ * Forward writes out [batch, seq, heads*64] and the log-sum-exp per row (fp32 [batch,heads,seq]). */
+int dtb_attention_fwd(const void* qkv, void* out, float* lse, int batch, int seq, int heads, int head_dim,
+                      void* stream);
+/* Backward: dqkv [batch, seq, 3*heads*64].  `scratch` must hold
+ * dtb_attention_bwd_scratch_floats(...) floats (fp32 dQ accumulator + row deltas). */
+size_t dtb_attention_bwd_scratch_floats(int batch, int seq, int heads, int head_dim);
+int dtb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                      float* scratch, int batch, int seq, int heads, int head_dim, void* stream);
+
+/* ---- optimizers (K13: torch.optim.SGD foreach kernels,
+ *      /root/reference/src/distributed_trainer.py:165,200) -------------------- */
+#define DTB_MT_MAX_TENSORS 48
+typedef struct dtb_mt_args {
+  void* param[DTB_MT_MAX_TENSORS];       /* bf16 or fp32 */
+  const void* grad[DTB_MT_MAX_TENSORS];  /* bf16 or fp32 */
+  float* master[DTB_MT_MAX_TENSORS];     /* optional fp32 master weights (NULL entries allowed if master_on=0) */
+  float* m[DTB_MT_MAX_TENSORS];          /* momentum / exp_avg (fp32) or NULL */
+  float* v[DTB_MT_MAX_TENSORS];          /* exp_avg_sq (fp32) or NULL */
+  long long numel[DTB_MT_MAX_TENSORS];
+  int count;
+  int param_fp32, grad_fp32, master_on;
+} dtb_mt_args;
+int dtb_multi_tensor_sgd(const dtb_mt_args* args, float lr, float momentum, float weight_decay, void* stream);
+int dtb_multi_tensor_adamw(const dtb_mt_args* args, float lr, float beta1, float beta2, float eps, float weight_decay,
+                           float bias_corr1, float bias_corr2, void* stream);
+
+/* ---- symmetric-memory collectives (K2-K8: NCCL broadcast / all-reduce / all-gather /
+ *      reduce-scatter issued by torch DDP / FSDP in the reference) ----------------
+ * A communicator is described by the table of every rank's mapping of the same
+ * symmetric allocation.  `peers[r]` is rank r's heap base as mapped in THIS process;
+ * `signals[r]` likewise for the signal pad (DTB_SIGNAL_PAD_BYTES, zero-initialised).
+ * Operands are given as byte offsets into the heap, identical on all ranks.
+ * `max_ctas` arguments: low 16 bits cap the grid (0 = default 32, at most 64 CTAs of 512 threads — the
+ * SM budget left to concurrently running GEMMs); bits 16..19 select the barrier channel (0..15).
+ * Kernels that may run concurrently on different streams must use different channels; every rank
+ * must issue the same sequence of collectives with the same arguments on a given channel. */
+#define DTB_MAX_RANKS 8
+#define DTB_SIGNAL_PAD_BYTES (64 * 1024)
+typedef struct dtb_comm {
+  void* peers[DTB_MAX_RANKS];
+  uint32_t* signals[DTB_MAX_RANKS];
+  void* mc_base;          /* NVLS multicast mapping of the heap, or NULL */
+  int rank, world;
+  long long timeout_cycles; /* spin watchdog (0 = default); on expiry the kernel sets an error flag and exits */
+} dtb_comm;
+/* all ranks enter; returns when every rank's prior work on `stream` is visible to peers */
+int dtb_comm_barrier(const dtb_comm* c, int channel, void* stream);
+/* buf[offset .. +bytes) on every rank = root's */
+int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes, int root, int max_ctas, void* stream);
+/* in-place mean over ranks of n elements at `offset` (dtype: 0 bf16, 1 fp32); algo: 0 auto, 1 one-shot,
+ * 2 two-shot, 3 NVLS multimem */
+int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long long n, int dtype, int algo, int max_ctas,
+                            void* stream);
+/* dst[r*n .. (r+1)*n) = rank r's src[0..n)  (element size esize) */
+int dtb_comm_all_gather(const dtb_comm* c, size_t dst_offset, size_t src_offset, long long n, int esize,
+                        int max_ctas, void* stream);
+/* out[0..n) (local, fp32 or bf16) = mean_r(rank r's src[rank*n .. (rank+1)*n)) */
+int dtb_comm_reduce_scatter_avg(const dtb_comm* c, void* out, int out_fp32, size_t src_offset, long long n,
+                                int src_dtype, int max_ctas, void* stream);
+/* fused reduce-scatter + optimizer on the local shard (K7+K13):
+ * g = mean_r(grad@r[rank*n..]); update master/moments; write bf16 shard at shard_offset. opt: 0 sgd, 1 adamw */
+int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t shard_offset, float* master, float* m,
+                      float* v, long long n, int opt, float lr, float beta1, float beta2, float eps,
+                      float weight_decay, float bias_corr1, float bias_corr2, float momentum, int max_ctas,
+                      void* stream);
+/* error flag raised by a spin watchdog (0 = none); host-synchronous */
+int dtb_comm_error_flag(const dtb_comm* c);
+
+/* ---- host-side helpers for the symmetric heap --------------------------------- */
+/* cudaMalloc + cudaIpcGetMemHandle; handle_out must hold 64 bytes. Allocates device memory. */
+int dtb_symm_alloc(size_t bytes, void** ptr_out, void* handle_out);
+int dtb_symm_open(const void* handle, void** ptr_out);
+int dtb_symm_close(void* ptr);
+int dtb_symm_free(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTB200_H_ */

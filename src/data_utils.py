@@ -1,0 +1,9 @@
+"""Datasets and sharding under the reference's module name (``src.data_utils``)."""
+from distributed_training_b200.data import (  # noqa: F401
+    LinearTeacherDataset,
+    MyTrainDataset,
+    ShardedLoader,
+    ShardedSampler,
+    TokenDataset,
+    WideDataset,
+)

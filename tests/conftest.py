@@ -1,0 +1,49 @@
+import os
+import socket
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run with `-m gpu` on a B200)")
+    config.addinivalue_line("markers", "multigpu: needs at least two CUDA devices")
+
+
+def pytest_collection_modifyitems(config, items):
+    try:
+        import torch
+
+        n_gpu = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    except Exception:  # pragma: no cover
+        n_gpu = 0
+    skip_gpu = pytest.mark.skip(reason="no CUDA device")
+    skip_multi = pytest.mark.skip(reason="needs >= 2 CUDA devices")
+    for item in items:
+        if "gpu" in item.keywords and n_gpu == 0:
+            item.add_marker(skip_gpu)
+        if "multigpu" in item.keywords and n_gpu < 2:
+            item.add_marker(skip_multi)
+
+
+def free_port() -> int:
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.fixture
+def port():
+    return free_port()
+
+
+@pytest.fixture(autouse=True)
+def _clean_dist_env(monkeypatch):
+    for var in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        monkeypatch.delenv(var, raising=False)
+    yield
