@@ -1,0 +1,265 @@
+#!/usr/bin/env python
+"""Headline benchmark: samples/sec of the wide-MLP (8 x 8192, bf16) DDP training step.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--batch B]
+
+N > 1 is launched by ``python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...``
+(one rank per GPU; RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* from the environment).
+
+Own arm      : distributed_training_b200 ``Trainer`` + ``DDPStrategy`` (peer-memory all-reduce, tcgen05 GEMMs).
+Reference arm: the UNMODIFIED reference ``Trainer`` / ``DDPStrategy`` from ``baseline/_ref`` (torch DDP + NCCL
+               + cuBLAS) on a plain-torch model of the same architecture.
+
+Both arms time exactly K steps after W warm-up steps with CUDA events, a barrier + synchronize on both
+sides, max over ranks, and print ONE JSON line on rank 0.  Weak scaling: the per-GPU batch is fixed.
+Data is synthetic, weights are random-init.  The step's working set (1 GiB of bf16 weights + activations)
+is far larger than the 126 MB L2, so no explicit flush is needed between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WIDTH, DEPTH = 8192, 8
+METRIC = "samples/sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--batch", type=int, default=4096, help="per-GPU batch (weak scaling)")
+    ap.add_argument("--lr", type=float, default=1e-4)
+    ap.add_argument("--width", type=int, default=WIDTH)
+    ap.add_argument("--depth", type=int, default=DEPTH)
+    ap.add_argument("--comm-ctas", type=int, default=0)
+    return ap.parse_args()
+
+
+def dist_env(args):
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world == 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+        os.environ.setdefault("RANK", "0")
+        os.environ.setdefault("LOCAL_RANK", "0")
+        os.environ.setdefault("WORLD_SIZE", "1")
+    if world != args.gpus:
+        if rank == 0:
+            print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run",
+                  file=sys.stderr)
+        args.gpus = world
+    return rank, local_rank, world
+
+
+def pinned_pool(batch, width, n=4, seed=0):
+    import torch
+
+    g = torch.Generator().manual_seed(seed)
+    pool = []
+    for _ in range(n):
+        x = torch.randn(batch, width, generator=g).to(torch.bfloat16).pin_memory()
+        y = torch.randint(0, width, (batch,), generator=g, dtype=torch.int64).pin_memory()
+        pool.append((x, y))
+    return pool
+
+
+def result_line(args, world, ms_per_step, e2e_ms_per_step, clocks, launches, impl, h2d, d2h, extra=None):
+    global_batch = args.batch * world
+    value = global_batch / (ms_per_step / 1e3)
+    line = {
+        "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": impl,
+        "config": {"model": f"wide MLP {args.depth}x{args.width} bf16 (Linear+GELU(tanh), CE over {args.width} classes)",
+                   "global_batch": global_batch, "per_gpu_batch": args.batch, "seq_len": None,
+                   "parallelism": f"dp{world}", "optimizer": "SGD (bf16 params, no momentum)",
+                   "l2": "working set (1 GiB weights + activations) >> 126 MB L2; no explicit flush"},
+        "clocks": clocks,
+        "e2e": {"value": global_batch / (e2e_ms_per_step / 1e3) if e2e_ms_per_step else None, "unit": "samples/s",
+                "ms_per_step": e2e_ms_per_step, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+    }
+    if extra:
+        line.update(extra)
+    return line
+
+
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from distributed_training_b200.models.mlp import MLP
+    from distributed_training_b200.ops import native
+    from distributed_training_b200.parallel.ddp import DDPStrategy
+    from distributed_training_b200.parallel.strategy import OptimizerSpec
+    from distributed_training_b200.trainer import DistributedEnvironment, Trainer, TrainingConfig
+    from distributed_training_b200.utils.clocks import ClockSampler
+    from distributed_training_b200.utils.timing import barrier_sync, max_over_ranks, time_steps_ms
+
+    rank, local_rank, world = dist_env(args)
+    native.require()
+    env = DistributedEnvironment("cuda")
+    env.setup()
+    device = env.torch_device
+    torch.manual_seed(0)
+    model = MLP(args.width, args.width, args.width, args.depth, dtype=torch.bfloat16)
+    cfg = TrainingConfig(max_epochs=1, save_every=10 ** 9, batch_size=args.batch, learning_rate=args.lr,
+                         snapshot_path=Path("/nonexistent/bench_snapshot.pt"), device="cuda",
+                         parallel_strategy="ddp", loss="cross_entropy", optimizer="sgd")
+    strategy = DDPStrategy(local_rank, True)
+    trainer = Trainer(model, [], OptimizerSpec("sgd", lr=args.lr), cfg, env, strategy=strategy)
+    if args.comm_ctas and strategy.comm is not None:
+        strategy.comm.comm_ctas = args.comm_ctas
+    assert trainer.model.native_step, "the native tcgen05 path must be the one that runs"
+
+    pool = pinned_pool(args.batch, args.width)
+    dev_pool = [(x.to(device), y.to(device)) for x, y in pool]
+
+    def step_dev(i):
+        x, y = dev_pool[i % len(dev_pool)]
+        trainer._run_batch(x, y)
+
+    for i in range(args.warmup):
+        step_dev(i)
+    native.reset_launch_count()
+    with ClockSampler(local_rank) as sampler:
+        total_ms = time_steps_ms(step_dev, args.steps)
+    launches = native.launch_count()
+    clocks = sampler.summary()
+    exposed = trainer.model.exposed_comm_ms() if hasattr(trainer.model, "exposed_comm_ms") else 0.0
+    exposed = max_over_ranks(exposed)
+    loss_val = float(trainer.last_loss)
+
+    # end to end through the public API: pinned host batch -> H2D -> step -> D2H loss, every step
+    def step_e2e(i):
+        x, y = pool[i % len(pool)]
+        loss = trainer.train_step(x, y)
+        return loss.item()
+
+    for i in range(2):
+        step_e2e(i)
+    barrier_sync()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for i in range(args.steps):
+        step_e2e(i)
+    stop.record()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks(start.elapsed_time(stop))
+    barrier_sync()
+
+    if rank == 0:
+        x, y = pool[0]
+        line = result_line(args, world, total_ms / args.steps, e2e_ms / args.steps, clocks, launches, "ours",
+                           x.numel() * x.element_size() + y.numel() * y.element_size(), 4,
+                           extra={"exposed_comm_ms_per_step": exposed, "final_loss": loss_val})
+        print(json.dumps(line), flush=True)
+    if strategy.comm is not None:
+        strategy.comm.close()
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------
+def run_reference(args):
+    from baseline.ref_loader import load_reference, reference_available
+
+    why = reference_available()
+    if why:
+        print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+        return
+    rank, local_rank, world = dist_env(args)
+    import torch
+    import torch.distributed as dist
+
+    try:
+        ref = load_reference()
+    except Exception as exc:  # noqa: BLE001
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": f"import failed: {exc}"[:200]}), flush=True)
+        return
+    from baseline.models import PooledClassificationDataset, wide_mlp_torch
+    from distributed_training_b200.utils.clocks import ClockSampler
+    from distributed_training_b200.utils.timing import barrier_sync, max_over_ranks, time_steps_ms
+
+    env = ref.DistributedEnvironment("cuda")
+    env.setup()                                           # init_process_group("nccl") + set_device
+    torch.manual_seed(0)
+    model = wide_mlp_torch(args.width, args.depth, torch.bfloat16)
+    optimizer = torch.optim.SGD(model.parameters(), lr=args.lr)
+    cfg = ref.TrainingConfig(max_epochs=1, save_every=10 ** 9, batch_size=args.batch, learning_rate=args.lr,
+                             snapshot_path=Path("/nonexistent/bench_snapshot.pt"), device="cuda",
+                             parallel_strategy="ddp")
+    e2e_steps = args.steps + 2
+    dataset = PooledClassificationDataset(e2e_steps * args.batch * world, args.width, args.width, torch.bfloat16)
+    loader = ref.prepare_dataloader(dataset, args.batch)   # DataLoader(pin_memory=True, DistributedSampler)
+    trainer = ref.Trainer(model, loader, optimizer, cfg, env)
+    device = torch.device("cuda", local_rank)
+
+    g = torch.Generator().manual_seed(0)
+    dev_pool = [(torch.randn(args.batch, args.width, generator=g).to(torch.bfloat16).to(device),
+                 torch.randint(0, args.width, (args.batch,), generator=g).to(device)) for _ in range(4)]
+
+    def step_dev(i):
+        x, y = dev_pool[i % len(dev_pool)]
+        trainer._run_batch(x, y)                           # the reference's own step
+
+    for i in range(args.warmup):
+        step_dev(i)
+    with ClockSampler(local_rank) as sampler:
+        total_ms = time_steps_ms(step_dev, args.steps)
+    clocks = sampler.summary()
+
+    # end to end = the body of the reference's Trainer._run_epoch on its own DataLoader, plus a 4-byte
+    # read-back of the step's result (the reference never exposes its loss, so a parameter element stands in)
+    probe = next(trainer.model.parameters())
+    loader.sampler.set_epoch(0)
+    it = iter(loader)
+    timed = 0
+    e2e_ms = None
+    bytes_in = 0
+    for i in range(e2e_steps):
+        source, targets = next(it)
+        if i == 2:
+            barrier_sync()
+            start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            start.record()
+        bytes_in = source.numel() * source.element_size() + targets.numel() * targets.element_size()
+        source = source.to(local_rank)
+        targets = targets.to(local_rank)
+        trainer._run_batch(source, targets)
+        probe.view(-1)[0].item()
+        timed += int(i >= 2)
+    stop.record()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks(start.elapsed_time(stop))
+    barrier_sync()
+
+    if rank == 0:
+        line = result_line(args, world, total_ms / args.steps, e2e_ms / max(timed, 1), clocks, 0, "reference",
+                           bytes_in, probe.element_size(),
+                           extra={"gpu_launches_note": "reference arm: torch/cuBLAS/NCCL kernels only"})
+        print(json.dumps(line), flush=True)
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    ns = parse_args()
+    if ns.impl == "reference":
+        run_reference(ns)
+    else:
+        run_ours(ns)

@@ -1,0 +1,306 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op
+(SURVEY §4.3 "kernel correctness" tier).  Run on a B200 with ``pytest -m gpu``."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from distributed_training_b200.ops import native
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _bf16(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(torch.bfloat16).to(DEV)
+
+
+def test_library_loaded_on_gpu_box():
+    assert native.available(), "libdtb200.so must be present on a GPU machine (python -m distributed_training_b200._native)"
+    assert native.lib().dtb_version() >= 100
+
+
+# ------------------------------------------------------------------------ GEMM
+def _gemm_ref(a, b, a_mn, b_mn):
+    A = a.float().t() if a_mn else a.float()          # logical [M,K]
+    B = b.float().t() if b_mn else b.float()          # logical [N,K]
+    return A @ B.t()
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("cta_pair,tile_n", [(1, 128), (1, 256), (2, 256)])
+@pytest.mark.parametrize("m,n,k", [(256, 512, 256), (384, 320, 200), (1024, 768, 1024)])
+def test_gemm_layouts_and_tiles(a_mn, b_mn, cta_pair, tile_n, m, n, k):
+    a = _bf16(*((k, m) if a_mn else (m, k)), seed=1)
+    b = _bf16(*((k, n) if b_mn else (n, k)), seed=2)
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    native.gemm(a, b, out, m=m, n=n, k=k, a_mn=a_mn, b_mn=b_mn, cta_pair=cta_pair, tile_n=tile_n)
+    ref = _gemm_ref(a, b, a_mn, b_mn)
+    torch.cuda.synchronize()
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 0.02 * math.sqrt(k) + 0.1 * ref.abs().max().item() / 32, f"max err {err}"
+    assert torch.allclose(out.float(), ref, atol=0.25, rtol=2e-2)
+
+
+def test_gemm_bias_gelu_epilogue_and_preactivation():
+    m, n, k = 512, 1024, 512
+    x, w = _bf16(m, k, seed=3), _bf16(n, k, scale=0.05, seed=4)
+    bias = _bf16(n, seed=5)
+    h = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    z = torch.empty_like(h)
+    native.gemm(x, w, h, m=m, n=n, k=k, bias=bias, act=1, d2=z)
+    zr = x.float() @ w.float().t() + bias.float()
+    assert torch.allclose(z.float(), zr, atol=0.06, rtol=2e-2)
+    assert torch.allclose(h.float(), F.gelu(zr, approximate="tanh"), atol=0.06, rtol=2e-2)
+
+
+def test_gemm_dgelu_and_axpby_epilogues_fp32_out():
+    m, n, k = 256, 512, 384
+    dy, w = _bf16(m, k, seed=6), _bf16(k, n, scale=0.05, seed=7)       # dgrad: B stored [K,N]
+    zprev = _bf16(m, n, seed=8)
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    native.gemm(dy, w, out, m=m, n=n, k=k, b_mn=True, aux=zprev, act=2)
+    zf = zprev.float().requires_grad_(True)
+    (F.gelu(zf, approximate="tanh")).backward(dy.float() @ w.float())
+    assert torch.allclose(out.float(), zf.grad, atol=0.06, rtol=2e-2)
+    # accumulate into an fp32 buffer: D = 0.5*acc + 2*aux
+    acc = torch.randn(m, n, device=DEV)
+    res = torch.empty_like(acc)
+    native.gemm(dy, w, res, m=m, n=n, k=k, b_mn=True, aux=acc, alpha=0.5, beta=2.0)
+    assert torch.allclose(res, 0.5 * (dy.float() @ w.float()) + 2 * acc, atol=0.05, rtol=1e-2)
+
+
+def test_gemm_batched_strided_heads():
+    # attention-style: per (batch, head) problem carved out of a packed [B, T, 3C] tensor
+    B, T, H, D = 2, 256, 3, 64
+    C3 = 3 * H * D
+    qkv = _bf16(B, T, C3, seed=9)
+    s = torch.empty(B, H, T, T, dtype=torch.bfloat16, device=DEV)
+    q, kk = qkv, qkv[:, :, H * D:]
+    native.gemm(q, kk, s, m=T, n=T, k=D, lda=C3, ldb=C3, ldd=T, batch=(H, B), a_strides=(D, T * C3),
+                b_strides=(D, T * C3), d_strides=(T * T, H * T * T), alpha=0.125)
+    qh = qkv[:, :, :H * D].view(B, T, H, D).permute(0, 2, 1, 3).float()
+    kh = qkv[:, :, H * D:2 * H * D].view(B, T, H, D).permute(0, 2, 1, 3).float()
+    ref = 0.125 * qh @ kh.transpose(-1, -2)
+    assert torch.allclose(s.float(), ref, atol=0.1, rtol=2e-2)
+
+
+def test_gemm_vocab_edge_tile():
+    m, n, k = 192, 50304 // 8, 128         # N not a multiple of the tile, M not a multiple of 128
+    a, b = _bf16(m, k, seed=10), _bf16(n, k, seed=11)
+    out = torch.full((m, n), float("nan"), dtype=torch.bfloat16, device=DEV)
+    native.gemm(a, b, out, m=m, n=n, k=k)
+    assert torch.allclose(out.float(), a.float() @ b.float().t(), atol=0.2, rtol=2e-2)
+
+
+def test_linear_small_matches_torch():
+    x = torch.randn(32, 20, device=DEV)
+    lin = torch.nn.Linear(20, 1).to(DEV)
+    y = torch.empty(32, 1, device=DEV)
+    native.linear_small_fwd(x, lin.weight.detach(), lin.bias.detach(), y)
+    assert torch.allclose(y, lin(x), atol=1e-5)
+    dy = torch.randn(32, 1, device=DEV)
+    dx, dw, db = torch.empty_like(x), torch.empty(1, 20, device=DEV), torch.empty(1, device=DEV)
+    native.linear_small_bwd(x, lin.weight.detach(), dy, dx, dw, db)
+    xr = x.clone().requires_grad_(True)
+    lin(xr).backward(dy)
+    assert torch.allclose(dx, xr.grad, atol=1e-5) and torch.allclose(dw, lin.weight.grad, atol=1e-4)
+    assert torch.allclose(db, lin.bias.grad, atol=1e-4)
+
+
+# ------------------------------------------------------------------- elementwise
+@pytest.mark.parametrize("n", [8, 1000, 4096 * 33 + 5])
+def test_gelu_add_cast(n):
+    x, dy = _bf16(n, seed=1), _bf16(n, seed=2)
+    y = torch.empty_like(x)
+    native.gelu_fwd(x, y)
+    assert torch.allclose(y.float(), F.gelu(x.float(), approximate="tanh"), atol=2e-2, rtol=2e-2)
+    dx = torch.empty_like(x)
+    native.gelu_bwd(x, dy, dx)
+    xr = x.float().requires_grad_(True)
+    F.gelu(xr, approximate="tanh").backward(dy.float())
+    assert torch.allclose(dx.float(), xr.grad, atol=3e-2, rtol=2e-2)
+    s = torch.empty_like(x)
+    native.add(x, dy, s)
+    assert torch.equal(s, (x.float() + dy.float()).to(torch.bfloat16))
+    f = torch.randn(n, device=DEV)
+    b = torch.empty(n, dtype=torch.bfloat16, device=DEV)
+    native.cast_f32_to_bf16(f, b)
+    assert torch.equal(b, f.to(torch.bfloat16))
+    back = torch.empty(n, device=DEV)
+    native.cast_bf16_to_f32(b, back)
+    assert torch.equal(back, b.float())
+
+
+@pytest.mark.parametrize("rows,cols", [(4096, 8192), (100, 72), (33, 1600)])
+def test_colsum_and_sumsq_and_mean(rows, cols):
+    x = _bf16(rows, cols, seed=3)
+    out = torch.empty(cols, dtype=torch.float32, device=DEV)
+    native.colsum(x, out)
+    assert torch.allclose(out, x.float().sum(0), atol=1e-2 * math.sqrt(rows), rtol=1e-3)
+    outb = torch.empty(cols, dtype=torch.bfloat16, device=DEV)
+    native.colsum(x, outb)
+    assert torch.allclose(outb.float(), x.float().sum(0), atol=0.5, rtol=2e-2)
+    acc = torch.zeros((), device=DEV)
+    native.sumsq(x, acc)
+    assert torch.allclose(acc, (x.float() ** 2).sum(), rtol=1e-3)
+    m = torch.empty((), device=DEV)
+    native.mean_f32(out, m)
+    assert torch.allclose(m, out.mean(), rtol=1e-4, atol=1e-4)
+
+
+# --------------------------------------------------------------------- layernorm
+@pytest.mark.parametrize("rows,cols", [(2048, 768), (512, 1600), (77, 1024), (64, 4096)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layernorm_fwd(rows, cols, with_res):
+    x, r = _bf16(rows, cols, seed=1), _bf16(rows, cols, seed=2)
+    g, b = _bf16(cols, seed=3) * 0.1 + 1, _bf16(cols, seed=4) * 0.1
+    y, xres = torch.empty_like(x), torch.empty_like(x)
+    mean, rstd = torch.empty(rows, device=DEV), torch.empty(rows, device=DEV)
+    native.layernorm_fwd(x, r if with_res else None, g, b, y, xres if with_res else None, mean, rstd)
+    xin = (x.float() + r.float()).to(torch.bfloat16).float() if with_res else x.float()
+    ref = F.layer_norm(xin, (cols,), g.float(), b.float(), 1e-5)
+    assert torch.allclose(y.float(), ref, atol=3e-2, rtol=2e-2)
+    assert torch.allclose(mean, xin.mean(-1), atol=1e-3)
+    assert torch.allclose(rstd, 1 / torch.sqrt(xin.var(-1, unbiased=False) + 1e-5), rtol=1e-3)
+    if with_res:
+        assert torch.equal(xres, xin.to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("rows,cols", [(2048, 768), (300, 1600)])
+def test_layernorm_bwd(rows, cols):
+    x, dy, dres = _bf16(rows, cols, seed=1), _bf16(rows, cols, seed=2), _bf16(rows, cols, seed=5)
+    g, b = _bf16(cols, seed=3) * 0.1 + 1, _bf16(cols, seed=4) * 0.1
+    y = torch.empty_like(x)
+    mean, rstd = torch.empty(rows, device=DEV), torch.empty(rows, device=DEV)
+    native.layernorm_fwd(x, None, g, b, y, None, mean, rstd)
+    dx = torch.empty_like(x)
+    dgamma, dbeta = torch.empty(cols, device=DEV), torch.empty(cols, device=DEV)
+    scratch = torch.empty(native.layernorm_bwd_scratch_floats(rows, cols), device=DEV)
+    native.layernorm_bwd(dy, x, g, mean, rstd, dres, dx, dgamma, dbeta, scratch)
+    xr, gr, br = x.float().requires_grad_(True), g.float().requires_grad_(True), b.float().requires_grad_(True)
+    F.layer_norm(xr, (cols,), gr, br, 1e-5).backward(dy.float())
+    assert torch.allclose(dx.float(), xr.grad + dres.float(), atol=6e-2, rtol=3e-2)
+    assert torch.allclose(dgamma, gr.grad, atol=2e-2 * math.sqrt(rows), rtol=1e-2)
+    assert torch.allclose(dbeta, br.grad, atol=2e-2 * math.sqrt(rows), rtol=1e-2)
+
+
+# ------------------------------------------------------------------------ losses
+@pytest.mark.parametrize("rows,vocab,ld", [(256, 8192, 8192), (64, 50257, 50304), (33, 1000, 1000)])
+def test_cross_entropy_fused(rows, vocab, ld):
+    logits = _bf16(rows, ld, scale=2.0, seed=1)
+    targets = torch.randint(0, vocab, (rows,), device=DEV)
+    ref_in = logits[:, :vocab].float().requires_grad_(True)
+    ref_loss = F.cross_entropy(ref_in, targets, reduction="none")
+    ref_loss.mean().backward()
+    row_loss = torch.empty(rows, device=DEV)
+    work = logits.clone()
+    native.cross_entropy_fwd_bwd(work, targets, row_loss, vocab, 1.0 / rows)
+    assert torch.allclose(row_loss, ref_loss, atol=2e-3, rtol=1e-3)
+    assert torch.allclose(work[:, :vocab].float(), ref_in.grad, atol=2e-3 / rows + 1e-5, rtol=2e-2)
+    if ld > vocab:
+        assert float(work[:, vocab:].float().abs().max()) == 0.0
+
+
+def test_soft_cross_entropy_and_mse():
+    x = torch.randn(32, 1, device=DEV)
+    t = torch.rand(32, 1, device=DEV)
+    row, d = torch.empty(32, device=DEV), torch.empty_like(x)
+    native.soft_cross_entropy_fwd_bwd(x, t, row, d, 1.0 / 32)
+    assert float(row.abs().max()) == 0.0 and float(d.abs().max()) == 0.0       # reference quirk Q1
+    x = torch.randn(16, 10, device=DEV)
+    t = torch.softmax(torch.randn(16, 10, device=DEV), -1)
+    row, d = torch.empty(16, device=DEV), torch.empty_like(x)
+    native.soft_cross_entropy_fwd_bwd(x, t, row, d, 1.0 / 16)
+    xr = x.clone().requires_grad_(True)
+    F.cross_entropy(xr, t).backward()
+    assert torch.allclose(row.mean(), F.cross_entropy(x, t), atol=1e-5)
+    assert torch.allclose(d, xr.grad, atol=1e-6)
+    p, tt = torch.randn(1000, device=DEV), torch.randn(1000, device=DEV)
+    s, dp = torch.empty((), device=DEV), torch.empty_like(p)
+    native.mse_fwd_bwd(p, tt, s, dp, 1.0 / 1000)
+    assert torch.allclose(s / 1000, F.mse_loss(p, tt), rtol=1e-5)
+    assert torch.allclose(dp, 2 * (p - tt) / 1000, atol=1e-7)
+
+
+# --------------------------------------------------------------------- embedding
+def test_embedding_fwd_bwd():
+    B, T, C, V = 4, 64, 768, 1000
+    wte, wpe = _bf16(V, C, seed=1), _bf16(T, C, seed=2)
+    tok = torch.randint(0, V, (B, T), device=DEV)
+    out = torch.empty(B, T, C, dtype=torch.bfloat16, device=DEV)
+    native.embedding_fwd(tok, wte, wpe, out)
+    assert torch.equal(out, (wte[tok] + wpe[None]).to(torch.bfloat16))
+    dout = _bf16(B, T, C, seed=3)
+    dwte, dwpe = torch.zeros_like(wte), torch.empty_like(wpe)
+    native.embedding_bwd(dout, tok, dwte, dwpe)
+    ref = torch.zeros(V, C, device=DEV).index_add_(0, tok.view(-1), dout.float().view(-1, C))
+    assert torch.allclose(dwte.float(), ref, atol=0.15, rtol=3e-2)
+    assert torch.allclose(dwpe.float(), dout.float().sum(0), atol=0.05, rtol=2e-2)
+
+
+# -------------------------------------------------------------------- optimizers
+@pytest.mark.parametrize("pdtype,gdtype,master", [(torch.float32, torch.float32, False),
+                                                   (torch.bfloat16, torch.bfloat16, False),
+                                                   (torch.bfloat16, torch.bfloat16, True),
+                                                   (torch.bfloat16, torch.float32, True)])
+def test_fused_sgd_and_adamw(pdtype, gdtype, master):
+    from distributed_training_b200.optim import FusedAdamW, FusedSGD
+
+    shapes = [(1000,), (33, 7), (512, 512), (5,)]
+    for kind in ("sgd", "adamw"):
+        torch.manual_seed(0)
+        ps = [torch.randn(s, device=DEV).to(pdtype).requires_grad_(True) for s in shapes]
+        ref = [p.detach().float().clone().requires_grad_(True) for p in ps]
+        if kind == "sgd":
+            opt = FusedSGD(ps, lr=0.1, momentum=0.9, weight_decay=0.01, master_weights=master)
+            ropt = torch.optim.SGD(ref, lr=0.1, momentum=0.9, weight_decay=0.01)
+        else:
+            opt = FusedAdamW(ps, lr=1e-2, weight_decay=0.1, master_weights=master)
+            ropt = torch.optim.AdamW(ref, lr=1e-2, weight_decay=0.1)
+        for step in range(3):
+            for p, r in zip(ps, ref):
+                g = torch.randn(p.shape, device=DEV)
+                p.grad = g.to(gdtype)
+                r.grad = p.grad.float()
+            opt.step()
+            ropt.step()
+        tol = 1e-5 if pdtype == torch.float32 else (2e-2 if not master else 1e-2)
+        for p, r in zip(ps, ref):
+            assert torch.allclose(p.detach().float(), r.detach(), atol=tol, rtol=tol), (kind, pdtype, master)
+        if master and pdtype != torch.float32:
+            for p, r in zip(ps, ref):
+                assert torch.allclose(opt.state[p]["master"], r.detach(), atol=1e-5, rtol=1e-5)
+
+
+# ----------------------------------------------------------------- model-level
+def test_native_mlp_step_matches_autograd():
+    from distributed_training_b200.models.mlp import MLP
+
+    torch.manual_seed(0)
+    model = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16).to(DEV)
+    assert model.native_ready()
+    x = _bf16(192, 256, seed=1)
+    y = torch.randint(0, 384, (192,), device=DEV)
+    loss = model.forward_backward(x, y)
+    native_grads = [p.grad.float().clone() for p in model.parameters()]
+    for p in model.parameters():
+        p.grad = None
+    ref = MLP(256, 512, 384, num_layers=3, dtype=torch.float32).to(DEV)
+    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    ref_loss = F.cross_entropy(ref(x.float()), y)
+    ref_loss.backward()
+    assert abs(float(loss) - float(ref_loss)) < 3e-2
+    for g, p in zip(native_grads, ref.parameters()):
+        scale = p.grad.abs().max().item() + 1e-6
+        assert (g - p.grad).abs().max().item() <= 0.06 * scale + 1e-4
+
+
+def test_launch_counter_counts():
+    native.reset_launch_count()
+    x = _bf16(1024, seed=1)
+    native.gelu_fwd(x, torch.empty_like(x))
+    native.gelu_fwd(x, torch.empty_like(x))
+    assert native.launch_count() == 2
