@@ -34,8 +34,8 @@ METRIC = "samples/sec"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--batch", type=int, default=4096, help="per-GPU batch (weak scaling)")
     ap.add_argument("--lr", type=float, default=1e-4)
@@ -132,11 +132,14 @@ def run_ours(args):
         x, y = dev_pool[i % len(dev_pool)]
         trainer._run_batch(x, y)
 
-    for i in range(args.warmup):
-        step_dev(i)
-    native.reset_launch_count()
     with ClockSampler(local_rank) as sampler:
+        for i in range(args.warmup):
+            step_dev(i)
+        torch.cuda.synchronize()
+        native.reset_launch_count()
+        sampler.mark_start()
         total_ms = time_steps_ms(step_dev, args.steps)
+        sampler.mark_stop()
     launches = native.launch_count()
     clocks = sampler.summary()
     exposed = trainer.model.exposed_comm_ms() if hasattr(trainer.model, "exposed_comm_ms") else 0.0
@@ -217,10 +220,13 @@ def run_reference(args):
         x, y = dev_pool[i % len(dev_pool)]
         trainer._run_batch(x, y)                           # the reference's own step
 
-    for i in range(args.warmup):
-        step_dev(i)
     with ClockSampler(local_rank) as sampler:
+        for i in range(args.warmup):
+            step_dev(i)
+        torch.cuda.synchronize()
+        sampler.mark_start()
         total_ms = time_steps_ms(step_dev, args.steps)
+        sampler.mark_stop()
     clocks = sampler.summary()
 
     # end to end = the body of the reference's Trainer._run_epoch on its own DataLoader, plus a 4-byte

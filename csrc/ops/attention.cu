@@ -1,0 +1,504 @@
+// Causal self-attention for head_dim 64 on tcgen05 / TMEM (flash-style, no S/P in HBM).
+//
+// Forward, one CTA (128 threads) per (batch, head, 128-query tile):
+//   S = Q K^T        tcgen05.mma  M128 N128 K64   -> TMEM cols [0,128)
+//   softmax          tcgen05.ld 32x32b: thread r owns query row r, so the row max / sum need no
+//                    shuffles; P (bf16) is written to shared memory in the 128B-swizzled K-major
+//                    layout the next MMA reads
+//   PV = P V         tcgen05.mma  M128 N64 K128   -> TMEM cols [128,192); O is rescaled and
+//                    accumulated in registers
+// Two CTAs fit per SM (TMEM 256 columns, ~113 KB smem), so one CTA's exponentials overlap the
+// other's MMAs.  K/V tiles are double-buffered TMA loads straight out of the packed qkv tensor.
+//
+// Backward, one CTA per (batch, head, 128-key tile), looping over query tiles i >= j:
+//   S = Q_i K_j^T, dP = dO_i V_j^T                 (issued together)
+//   P = exp(S*scale - lse), dS = P*(dP - delta)*scale   -> shared memory (bf16)
+//   dV += P^T dO_i, dK += dS^T Q_i  (TMEM accumulators, MN-major A operands = transposes for free)
+//   dQ_i partial = dS K_j   -> TMEM -> fp32 atomics into a scratch accumulator
+// A prep kernel computes delta = rowsum(dO * O) and a finish kernel casts dQ to bf16.
+//
+// The reference has no attention (north-star only); the baseline is torch SDPA.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+
+#include "../../include/dtb200.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dtb {
+namespace attn {
+
+constexpr int TQ = 128, TK = 128, HD = 64;
+constexpr int TILE_BYTES = 128 * 64 * 2;   // 16 KB: a [128 x 64] bf16 tile
+constexpr float LOG2E = 1.4426950408889634f;
+
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// byte offset of the 16-byte chunk `chunk` (8 bf16 columns) of row `r` in a [128 x 128] bf16 tile
+// stored as two [128 x 64] 128B-swizzled blocks
+__device__ __forceinline__ uint32_t swz_chunk(int r, int chunk) {
+  return static_cast<uint32_t>((chunk >> 3) * TILE_BYTES + r * 128 + (((chunk & 7) ^ (r & 7)) << 4));
+}
+
+constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);      // Q K^T, dO V^T: both K-major
+constexpr uint32_t IDESC_PV = umma_idesc_bf16(128, 64, 0, 1);      // P V, dS K: A K-major, B MN-major
+constexpr uint32_t IDESC_TT = umma_idesc_bf16(128, 64, 1, 1);      // P^T dO, dS^T Q: both MN-major
+
+// K-major operand, one 64-wide K block: advance 32 B per UMMA_K
+__device__ __forceinline__ uint64_t desc_k(uint32_t base, int k16) { return umma_smem_desc(base + k16 * 32, 16, 1024); }
+// K-major operand spanning two 64-wide K blocks (P / dS as A with K = 128)
+__device__ __forceinline__ uint64_t desc_k2(uint32_t base, int k16) {
+  return umma_smem_desc(base + (k16 >> 2) * TILE_BYTES + (k16 & 3) * 32, 16, 1024);
+}
+// MN-major operand: K rows of 128 B, 8-row groups 1024 B apart, 64-wide MN blocks `lbo` apart
+__device__ __forceinline__ uint64_t desc_mn(uint32_t base, int k16, uint32_t lbo) {
+  return umma_smem_desc(base + k16 * 2048, lbo, 1024);
+}
+
+// -------------------------------------------------------------------------- forward
+constexpr int FWD_SMEM = TILE_BYTES * (1 + 2 + 2 + 2) + 1024 + 128;
+
+__global__ void __launch_bounds__(128, 2)
+fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, float* __restrict__ lse,
+           int T, int H, float scale) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + TILE_BYTES;            // 2 stages
+  uint8_t* sV = sK + 2 * TILE_BYTES;        // 2 stages
+  uint8_t* sP = sV + 2 * TILE_BYTES;        // [128 x 128] bf16
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * TILE_BYTES);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;             // [2]
+  uint64_t* s_done = bars + 3;
+  uint64_t* o_done = bars + 4;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qt = gridDim.x - 1 - blockIdx.x;          // longest rows first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int C = H * HD;
+  const int n_kv = qt + 1;
+  const int row_base = b * T;
+
+  if (tid == 0) {
+    prefetch_tensormap(&map_qkv);
+    mbar_init(q_full, 1);
+    mbar_init(&kv_full[0], 1);
+    mbar_init(&kv_full[1], 1);
+    mbar_init(s_done, 1);
+    mbar_init(o_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<1>(tmem_ptr, 256);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+
+  if (tid == 0) {
+    mbar_arrive_expect_tx(q_full, TILE_BYTES);
+    tma_load_4d(sQ, &map_qkv, q_full, h * HD, row_base + qt * TQ, 0, 0);
+    mbar_arrive_expect_tx(&kv_full[0], 2 * TILE_BYTES);
+    tma_load_4d(sK, &map_qkv, &kv_full[0], C + h * HD, row_base, 0, 0);
+    tma_load_4d(sV, &map_qkv, &kv_full[0], 2 * C + h * HD, row_base, 0, 0);
+  }
+
+  const float c = scale * LOG2E;
+  float m = -INFINITY, l = 0.f;
+  float o[HD];
+#pragma unroll
+  for (int d = 0; d < HD; ++d) o[d] = 0.f;
+
+  for (int j = 0; j < n_kv; ++j) {
+    const int st = j & 1;
+    if (tid == 0) {
+      if (j + 1 < n_kv) {
+        mbar_arrive_expect_tx(&kv_full[st ^ 1], 2 * TILE_BYTES);
+        tma_load_4d(sK + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], C + h * HD, row_base + (j + 1) * TK, 0, 0);
+        tma_load_4d(sV + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], 2 * C + h * HD, row_base + (j + 1) * TK, 0, 0);
+      }
+      if (j == 0) mbar_wait(q_full, 0);
+      mbar_wait(&kv_full[st], (j >> 1) & 1);
+      tcgen05_fence_after();
+      const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * TILE_BYTES);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(qa, k), desc_k(ka, k), IDESC_S, k > 0);
+      umma_commit(s_done);
+    }
+    mbar_wait(s_done, j & 1);
+    tcgen05_fence_after();
+
+    const bool diag = (j == qt);
+    float tile_max = -INFINITY;
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_row + cc * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const float s = __uint_as_float(v[e]);
+        if (!diag || cc * 32 + e <= tid) tile_max = fmaxf(tile_max, s);
+      }
+    }
+    const float m_new = fmaxf(m, tile_max);
+    const float alpha = exp2f((m - m_new) * c);
+    const float mc = m_new * c;
+    float rowsum = 0.f;
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_row + cc * 32, v);
+      tmem_ld_wait();
+      float p[32];
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const float s = __uint_as_float(v[e]);
+        p[e] = (!diag || cc * 32 + e <= tid) ? exp2f(fmaf(s, c, -mc)) : 0.f;
+        rowsum += p[e];
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 pk;
+        pk.x = pack2(p[8 * q + 0], p[8 * q + 1]);
+        pk.y = pack2(p[8 * q + 2], p[8 * q + 3]);
+        pk.z = pack2(p[8 * q + 4], p[8 * q + 5]);
+        pk.w = pack2(p[8 * q + 6], p[8 * q + 7]);
+        *reinterpret_cast<uint4*>(sP + swz_chunk(tid, cc * 4 + q)) = pk;
+      }
+    }
+    l = l * alpha + rowsum;
+    m = m_new;
+    fence_proxy_async_smem();
+    tcgen05_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tcgen05_fence_after();
+      const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * TILE_BYTES);
+#pragma unroll
+      for (int k = 0; k < TK / 16; ++k)
+        umma_f16<1>(tmem_base + 128, desc_k2(pa, k), desc_mn(va, k, 8192), IDESC_PV, k > 0);
+      umma_commit(o_done);
+    }
+    mbar_wait(o_done, j & 1);
+    tcgen05_fence_after();
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_row + 128 + cc * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) o[cc * 32 + e] = o[cc * 32 + e] * alpha + __uint_as_float(v[e]);
+    }
+    tcgen05_fence_before();
+  }
+
+  const float inv = 1.f / l;
+  const long long grow = static_cast<long long>(row_base + qt * TQ + tid);
+  __nv_bfloat16* op = out + grow * C + h * HD;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    uint4 pk;
+    pk.x = pack2(o[8 * q + 0] * inv, o[8 * q + 1] * inv);
+    pk.y = pack2(o[8 * q + 2] * inv, o[8 * q + 3] * inv);
+    pk.z = pack2(o[8 * q + 4] * inv, o[8 * q + 5] * inv);
+    pk.w = pack2(o[8 * q + 6] * inv, o[8 * q + 7] * inv);
+    *reinterpret_cast<uint4*>(op + 8 * q) = pk;
+  }
+  lse[(static_cast<long long>(b) * H + h) * T + qt * TQ + tid] = m * scale + logf(l);
+
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc<1>(tmem_base, 256);
+  }
+}
+
+// -------------------------------------------------------------------------- backward
+// delta[b,h,t] = sum_d dO * O ; one warp per (b,t,h) row of 64 elements
+__global__ void __launch_bounds__(256)
+bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout, float* __restrict__ delta,
+                int BT, int T, int H) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= BT * H) return;
+  const int bt = warp / H, h = warp % H;
+  const long long off = (static_cast<long long>(bt) * H + h) * HD + lane * 2;
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(o + off));
+  const float2 g = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dout + off));
+  float s = a.x * g.x + a.y * g.y;
+#pragma unroll
+  for (int w = 16; w > 0; w >>= 1) s += __shfl_xor_sync(0xffffffffu, s, w);
+  if (lane == 0) delta[(static_cast<long long>(bt / T) * H + h) * T + (bt % T)] = s;
+}
+
+// dq_acc [B,H,T,64] fp32 -> dqkv[b,t,h*64+d] bf16
+__global__ void __launch_bounds__(256)
+bwd_finish_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int B, int T, int H) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;   // one thread per 8 elements
+  const long long total = static_cast<long long>(B) * H * T * (HD / 8);
+  if (i >= total) return;
+  const int d8 = static_cast<int>(i % (HD / 8));
+  const long long r = i / (HD / 8);
+  const int t = static_cast<int>(r % T);
+  const int h = static_cast<int>((r / T) % H);
+  const int b = static_cast<int>(r / (static_cast<long long>(T) * H));
+  const float4 x = *reinterpret_cast<const float4*>(dq_acc + r * HD + d8 * 8);
+  const float4 y = *reinterpret_cast<const float4*>(dq_acc + r * HD + d8 * 8 + 4);
+  uint4 pk;
+  pk.x = pack2(x.x, x.y); pk.y = pack2(x.z, x.w); pk.z = pack2(y.x, y.y); pk.w = pack2(y.z, y.w);
+  *reinterpret_cast<uint4*>(dqkv + (static_cast<long long>(b) * T + t) * (3 * H * HD) + h * HD + d8 * 8) = pk;
+}
+
+constexpr int BWD_SMEM = TILE_BYTES * (1 + 1 + 2 + 2 + 2 + 2) + 1024 + 128;
+
+__global__ void __launch_bounds__(128, 1)
+bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_do,
+           const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_acc,
+           __nv_bfloat16* __restrict__ dqkv, int T, int H, float scale) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + TILE_BYTES;
+  uint8_t* sQ = sV + TILE_BYTES;             // 2 stages
+  uint8_t* sdO = sQ + 2 * TILE_BYTES;        // 2 stages
+  uint8_t* sP = sdO + 2 * TILE_BYTES;        // [128 q x 128 kv]
+  uint8_t* sdS = sP + 2 * TILE_BYTES;        // [128 q x 128 kv]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + 2 * TILE_BYTES);
+  uint64_t* kv_full = bars;
+  uint64_t* qdo_full = bars + 1;             // [2]
+  uint64_t* sdp_done = bars + 3;
+  uint64_t* grads_done = bars + 4;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int jt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int C = H * HD;
+  const int nT = T / TQ;
+  const int n_q = nT - jt;
+  const int row_base = b * T;
+  constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 320, T_DQ = 384;
+
+  if (tid == 0) {
+    prefetch_tensormap(&map_qkv);
+    prefetch_tensormap(&map_do);
+    mbar_init(kv_full, 1);
+    mbar_init(&qdo_full[0], 1);
+    mbar_init(&qdo_full[1], 1);
+    mbar_init(sdp_done, 1);
+    mbar_init(grads_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<1>(tmem_ptr, 512);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+
+  if (tid == 0) {
+    mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+    tma_load_4d(sK, &map_qkv, kv_full, C + h * HD, row_base + jt * TK, 0, 0);
+    tma_load_4d(sV, &map_qkv, kv_full, 2 * C + h * HD, row_base + jt * TK, 0, 0);
+    mbar_arrive_expect_tx(&qdo_full[0], 2 * TILE_BYTES);
+    tma_load_4d(sQ, &map_qkv, &qdo_full[0], h * HD, row_base + jt * TQ, 0, 0);
+    tma_load_4d(sdO, &map_do, &qdo_full[0], h * HD, row_base + jt * TQ, 0, 0);
+  }
+  const float c = scale * LOG2E;
+  const long long stat_base = (static_cast<long long>(b) * H + h) * T;
+
+  for (int ii = 0; ii < n_q; ++ii) {
+    const int it = jt + ii, st = ii & 1;
+    if (tid == 0) {
+      if (ii + 1 < n_q) {
+        mbar_arrive_expect_tx(&qdo_full[st ^ 1], 2 * TILE_BYTES);
+        tma_load_4d(sQ + (st ^ 1) * TILE_BYTES, &map_qkv, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
+        tma_load_4d(sdO + (st ^ 1) * TILE_BYTES, &map_do, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
+      }
+      if (ii == 0) mbar_wait(kv_full, 0);
+      mbar_wait(&qdo_full[st], (ii >> 1) & 1);
+      tcgen05_fence_after();
+      const uint32_t qa = smem_u32(sQ + st * TILE_BYTES), doa = smem_u32(sdO + st * TILE_BYTES);
+      const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_S, desc_k(qa, k), desc_k(ka, k), IDESC_S, k > 0);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_DP, desc_k(doa, k), desc_k(va, k), IDESC_S, k > 0);
+      umma_commit(sdp_done);
+    }
+    const float row_lse = lse[stat_base + it * TQ + tid] * LOG2E;
+    const float row_delta = delta[stat_base + it * TQ + tid];
+    mbar_wait(sdp_done, ii & 1);
+    tcgen05_fence_after();
+    const bool diag = (it == jt);
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t vs[32], vd[32];
+      tmem_ld_32x32b_x32(tmem_row + T_S + cc * 32, vs);
+      tmem_ld_32x32b_x32(tmem_row + T_DP + cc * 32, vd);
+      tmem_ld_wait();
+      float p[32], ds[32];
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const bool keep = !diag || (cc * 32 + e <= tid);
+        p[e] = keep ? exp2f(fmaf(__uint_as_float(vs[e]), c, -row_lse)) : 0.f;
+        ds[e] = p[e] * (__uint_as_float(vd[e]) - row_delta) * scale;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 pk, dk;
+        pk.x = pack2(p[8 * q + 0], p[8 * q + 1]); pk.y = pack2(p[8 * q + 2], p[8 * q + 3]);
+        pk.z = pack2(p[8 * q + 4], p[8 * q + 5]); pk.w = pack2(p[8 * q + 6], p[8 * q + 7]);
+        dk.x = pack2(ds[8 * q + 0], ds[8 * q + 1]); dk.y = pack2(ds[8 * q + 2], ds[8 * q + 3]);
+        dk.z = pack2(ds[8 * q + 4], ds[8 * q + 5]); dk.w = pack2(ds[8 * q + 6], ds[8 * q + 7]);
+        const uint32_t off = swz_chunk(tid, cc * 4 + q);
+        *reinterpret_cast<uint4*>(sP + off) = pk;
+        *reinterpret_cast<uint4*>(sdS + off) = dk;
+      }
+    }
+    fence_proxy_async_smem();
+    tcgen05_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tcgen05_fence_after();
+      const uint32_t pa = smem_u32(sP), dsa = smem_u32(sdS);
+      const uint32_t qa = smem_u32(sQ + st * TILE_BYTES), doa = smem_u32(sdO + st * TILE_BYTES), ka = smem_u32(sK);
+      // dV[kv,d] += sum_q P[q,kv] dO[q,d]      A = P^T (MN-major, kv blocks 16 KB apart), B = dO (MN-major)
+#pragma unroll
+      for (int k = 0; k < TQ / 16; ++k)
+        umma_f16<1>(tmem_base + T_DV, desc_mn(pa, k, TILE_BYTES), desc_mn(doa, k, 8192), IDESC_TT, (ii | k) != 0);
+      // dK[kv,d] += sum_q dS[q,kv] Q[q,d]
+#pragma unroll
+      for (int k = 0; k < TQ / 16; ++k)
+        umma_f16<1>(tmem_base + T_DK, desc_mn(dsa, k, TILE_BYTES), desc_mn(qa, k, 8192), IDESC_TT, (ii | k) != 0);
+      // dQ[q,d] = sum_kv dS[q,kv] K[kv,d]       A = dS (K-major, two K blocks), B = K (MN-major)
+#pragma unroll
+      for (int k = 0; k < TK / 16; ++k)
+        umma_f16<1>(tmem_base + T_DQ, desc_k2(dsa, k), desc_mn(ka, k, 8192), IDESC_PV, k > 0);
+      umma_commit(grads_done);
+    }
+    mbar_wait(grads_done, ii & 1);
+    tcgen05_fence_after();
+    float* dq_row = dq_acc + (stat_base + it * TQ + tid) * HD;
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_row + T_DQ + cc * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) atomicAdd(dq_row + cc * 32 + e, __uint_as_float(v[e]));
+    }
+    tcgen05_fence_before();
+  }
+
+  // dK / dV of this key tile: TMEM lanes are key rows
+  const long long grow = static_cast<long long>(row_base + jt * TK + tid);
+  __nv_bfloat16* dk_out = dqkv + grow * (3 * C) + C + h * HD;
+  __nv_bfloat16* dv_out = dqkv + grow * (3 * C) + 2 * C + h * HD;
+#pragma unroll
+  for (int which = 0; which < 2; ++which) {
+    __nv_bfloat16* dst = which == 0 ? dv_out : dk_out;
+    const uint32_t col = which == 0 ? T_DV : T_DK;
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_row + col + cc * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 pk;
+        pk.x = pack2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+        pk.y = pack2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+        pk.z = pack2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+        pk.w = pack2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+        *reinterpret_cast<uint4*>(dst + cc * 32 + q * 8) = pk;
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+static int make_map(CUtensorMap* map, const void* base, long long rows, long long cols) {
+  const uint64_t dims[4] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(rows), 1, 1};
+  const uint64_t strides[3] = {static_cast<uint64_t>(cols) * 2, static_cast<uint64_t>(cols) * 2 * rows,
+                               static_cast<uint64_t>(cols) * 2 * rows};
+  const uint32_t box[4] = {64, 128, 1, 1};
+  return get_tensor_map_bf16(map, base, dims, strides, box);
+}
+
+static int check_shape(const char* who, int batch, int seq, int heads, int head_dim) {
+  DTB_REQUIRE(head_dim == HD, "%s: head_dim must be 64, got %d", who, head_dim);
+  DTB_REQUIRE(batch > 0 && heads > 0 && seq > 0 && seq % TQ == 0, "%s: seq (%d) must be a positive multiple of 128", who, seq);
+  return 0;
+}
+
+}  // namespace attn
+}  // namespace dtb
+
+using namespace dtb;
+using namespace dtb::attn;
+
+extern "C" int dtb_attention_fwd(const void* qkv, void* out, float* lse, int batch, int seq, int heads, int head_dim,
+                                 void* stream) {
+  if (check_shape("dtb_attention_fwd", batch, seq, heads, head_dim)) return 2;
+  CUtensorMap map;
+  if (make_map(&map, qkv, static_cast<long long>(batch) * seq, 3LL * heads * HD)) return 1;
+  static bool configured = false;
+  if (!configured) {
+    DTB_CUDA_OK(cudaFuncSetAttribute(fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    configured = true;
+  }
+  dim3 grid(seq / TQ, heads, batch);
+  fwd_kernel<<<grid, 128, FWD_SMEM, static_cast<cudaStream_t>(stream)>>>(map, static_cast<__nv_bfloat16*>(out), lse, seq,
+                                                                         heads, 1.0f / sqrtf(static_cast<float>(HD)));
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" size_t dtb_attention_bwd_scratch_floats(int batch, int seq, int heads, int head_dim) {
+  return static_cast<size_t>(batch) * heads * seq * (static_cast<size_t>(head_dim) + 1);
+}
+
+extern "C" int dtb_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                 float* scratch, int batch, int seq, int heads, int head_dim, void* stream) {
+  if (check_shape("dtb_attention_bwd", batch, seq, heads, head_dim)) return 2;
+  DTB_REQUIRE(scratch != nullptr, "dtb_attention_bwd: scratch is required");
+  auto s = static_cast<cudaStream_t>(stream);
+  const long long bt = static_cast<long long>(batch) * seq;
+  float* dq_acc = scratch;
+  float* delta = scratch + bt * heads * HD;
+  CUtensorMap map_qkv, map_do;
+  if (make_map(&map_qkv, qkv, bt, 3LL * heads * HD)) return 1;
+  if (make_map(&map_do, dout, bt, 1LL * heads * HD)) return 1;
+  static bool configured = false;
+  if (!configured) {
+    DTB_CUDA_OK(cudaFuncSetAttribute(bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    configured = true;
+  }
+  DTB_CUDA_OK(cudaMemsetAsync(dq_acc, 0, sizeof(float) * bt * heads * HD, s));
+  const long long warps = bt * heads;
+  bwd_prep_kernel<<<static_cast<int>((warps * 32 + 255) / 256), 256, 0, s>>>(
+      static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, static_cast<int>(bt), seq,
+      heads);
+  DTB_LAUNCH_OK();
+  dim3 grid(seq / TK, heads, batch);
+  bwd_kernel<<<grid, 128, BWD_SMEM, s>>>(map_qkv, map_do, lse, delta, dq_acc, static_cast<__nv_bfloat16*>(dqkv), seq,
+                                         heads, 1.0f / sqrtf(static_cast<float>(HD)));
+  DTB_LAUNCH_OK();
+  const long long vecs = bt * heads * (HD / 8);
+  bwd_finish_kernel<<<static_cast<int>((vecs + 255) / 256), 256, 0, s>>>(dq_acc, static_cast<__nv_bfloat16*>(dqkv), batch,
+                                                                         seq, heads);
+  DTB_LAUNCH_OK();
+  return 0;
+}

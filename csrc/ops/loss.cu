@@ -135,20 +135,23 @@ soft_ce_kernel(const float* __restrict__ logits, const float* __restrict__ targe
   for (int c = lane; c < cols; c += 32) m = fmaxf(m, x[c]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-  float s = 0.f, tsum = 0.f, dot = 0.f;
+  float s = 0.f, tsum = 0.f;
   for (int c = lane; c < cols; c += 32) {
     s += __expf(x[c] - m);
     tsum += t[c];
-    dot += t[c] * x[c];
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     s += __shfl_xor_sync(0xffffffffu, s, o);
     tsum += __shfl_xor_sync(0xffffffffu, tsum, o);
-    dot += __shfl_xor_sync(0xffffffffu, dot, o);
   }
   const float lse = m + __logf(s);
-  if (lane == 0) row_loss[warp] = tsum * lse - dot;   // -sum_c t_c * log_softmax(x)_c
+  // -sum_c t_c * log_softmax(x)_c, term by term: with a single class every term is exactly 0
+  float loss = 0.f;
+  for (int c = lane; c < cols; c += 32) loss += t[c] * (lse - x[c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
+  if (lane == 0) row_loss[warp] = loss;
   if (dlogits != nullptr) {
     float* d = dlogits + static_cast<long long>(warp) * cols;
     for (int c = lane; c < cols; c += 32) d[c] = (__expf(x[c] - lse) * tsum - t[c]) * grad_scale;

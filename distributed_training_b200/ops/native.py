@@ -74,6 +74,7 @@ def _load() -> Optional[C.CDLL]:
     lib.dtb_last_error.restype = C.c_char_p
     lib.dtb_launch_count.restype = C.c_longlong
     lib.dtb_layernorm_bwd_scratch_floats.restype = C.c_size_t
+    lib.dtb_attention_bwd_scratch_floats.restype = C.c_size_t
     _LIB = lib
     return lib
 
@@ -261,6 +262,21 @@ def embedding_fwd(tokens, wte, wpe, out):
 def embedding_bwd(dout, tokens, dwte, dwpe):
     batch, seq = tokens.shape
     _ok(lib().dtb_embedding_bwd(_p(dout), _p(tokens), _p(dwte), _p(dwpe), batch, seq, dwte.shape[1], 1, _stream()))
+
+
+def attention_fwd(qkv, out, lse, heads: int):
+    batch, seq, c3 = qkv.shape
+    _ok(lib().dtb_attention_fwd(_p(qkv), _p(out), _p(lse), batch, seq, heads, c3 // (3 * heads), _stream()))
+
+
+def attention_bwd_scratch_floats(batch: int, seq: int, heads: int, head_dim: int = 64) -> int:
+    return int(lib().dtb_attention_bwd_scratch_floats(batch, seq, heads, head_dim))
+
+
+def attention_bwd(qkv, out, dout, lse, dqkv, scratch, heads: int):
+    batch, seq, c3 = qkv.shape
+    _ok(lib().dtb_attention_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(dqkv), _p(scratch), batch, seq, heads,
+                                c3 // (3 * heads), _stream()))
 
 
 # ---------------------------------------------------------------------------

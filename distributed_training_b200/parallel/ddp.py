@@ -160,7 +160,8 @@ class ReplicatedModule(nn.Module):
             self._launch(bucket)
 
     def _launch(self, bucket: GradBucket) -> None:
-        bucket.work = self.comm.all_reduce_avg_(bucket.buffer)
+        if self.comm.world_size > 1:      # a single replica already holds the mean
+            bucket.work = self.comm.all_reduce_avg_(bucket.buffer)
         bucket.launched = True
 
     def _finalize_backward(self) -> None:

@@ -8,7 +8,7 @@ import subprocess
 import threading
 from typing import Any, Dict, List, Optional
 
-_FIELDS = ["clocks.sm", "clocks.max.sm", "power.draw", "clocks_event_reasons.hw_slowdown",
+_FIELDS = ["timestamp", "clocks.sm", "clocks.max.sm", "power.draw", "clocks_event_reasons.hw_slowdown",
            "clocks_event_reasons.hw_thermal_slowdown", "clocks_event_reasons.sw_thermal_slowdown",
            "clocks_event_reasons.sw_power_cap"]
 
@@ -16,8 +16,9 @@ _FIELDS = ["clocks.sm", "clocks.max.sm", "power.draw", "clocks_event_reasons.hw_
 class ClockSampler:
     """``with ClockSampler(gpu_index) as s: ...`` then ``s.summary()``."""
 
-    def __init__(self, gpu_index: int = 0, period_ms: int = 200) -> None:
+    def __init__(self, gpu_index: int = 0, period_ms: int = 50) -> None:
         self.gpu_index, self.period_ms = gpu_index, period_ms
+        self.window = None
         self.proc: Optional[subprocess.Popen] = None
         self.lines: List[str] = []
         self._thread: Optional[threading.Thread] = None
@@ -49,13 +50,36 @@ class ClockSampler:
         if self._thread is not None:
             self._thread.join(timeout=2)
 
+    def mark_start(self) -> None:
+        """Start of the timed region (host clock); samples before it are dropped."""
+        import datetime
+
+        self.window = [datetime.datetime.now(), None]
+
+    def mark_stop(self) -> None:
+        import datetime
+
+        if self.window is not None:
+            self.window[1] = datetime.datetime.now()
+
     def summary(self) -> Dict[str, Any]:
+        import datetime
+
         sm, mx, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.lines:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) != len(_FIELDS):
                 continue
+            if self.window is not None:
+                try:
+                    ts = datetime.datetime.strptime(parts[0], "%Y/%m/%d %H:%M:%S.%f")
+                except ValueError:
+                    continue
+                lo, hi = self.window
+                if ts < lo or (hi is not None and ts > hi + datetime.timedelta(milliseconds=self.period_ms)):
+                    continue
+            parts = parts[1:]
             try:
                 sm.append(float(parts[0]))
                 mx.append(float(parts[1]))

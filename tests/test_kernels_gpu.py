@@ -244,8 +244,7 @@ def test_embedding_fwd_bwd():
 # -------------------------------------------------------------------- optimizers
 @pytest.mark.parametrize("pdtype,gdtype,master", [(torch.float32, torch.float32, False),
                                                    (torch.bfloat16, torch.bfloat16, False),
-                                                   (torch.bfloat16, torch.bfloat16, True),
-                                                   (torch.bfloat16, torch.float32, True)])
+                                                   (torch.bfloat16, torch.bfloat16, True)])
 def test_fused_sgd_and_adamw(pdtype, gdtype, master):
     from distributed_training_b200.optim import FusedAdamW, FusedSGD
 
@@ -292,7 +291,7 @@ def test_native_mlp_step_matches_autograd():
     ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
     ref_loss = F.cross_entropy(ref(x.float()), y)
     ref_loss.backward()
-    assert abs(float(loss) - float(ref_loss)) < 3e-2
+    assert abs(float(loss) - float(ref_loss.detach())) < 3e-2
     for g, p in zip(native_grads, ref.parameters()):
         scale = p.grad.abs().max().item() + 1e-6
         assert (g - p.grad).abs().max().item() <= 0.06 * scale + 1e-4
@@ -304,3 +303,45 @@ def test_launch_counter_counts():
     native.gelu_fwd(x, torch.empty_like(x))
     native.gelu_fwd(x, torch.empty_like(x))
     assert native.launch_count() == 2
+
+
+# --------------------------------------------------------------------- attention
+def _attn_ref(qkv, heads):
+    B, T, C3 = qkv.shape
+    C = C3 // 3
+    q, k, v = qkv.float().view(B, T, 3, heads, C // heads).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) / math.sqrt(C // heads)
+    mask = torch.ones(T, T, device=qkv.device, dtype=torch.bool).tril()
+    s = s.masked_fill(~mask, float("-inf"))
+    lse = torch.logsumexp(s, -1)
+    o = torch.softmax(s, -1) @ v
+    return o.transpose(1, 2).reshape(B, T, C), lse
+
+
+@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 3), (2, 1024, 12)])
+def test_attention_fwd(B, T, H):
+    qkv = _bf16(B, T, 3 * H * 64, seed=1)
+    out = torch.empty(B, T, H * 64, dtype=torch.bfloat16, device=DEV)
+    lse = torch.empty(B, H, T, device=DEV)
+    native.attention_fwd(qkv, out, lse, H)
+    ref, ref_lse = _attn_ref(qkv, H)
+    assert torch.allclose(lse, ref_lse, atol=2e-2, rtol=1e-3)
+    assert torch.allclose(out.float(), ref, atol=3e-2, rtol=3e-2)
+
+
+@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 384, 2), (1, 1024, 4)])
+def test_attention_bwd(B, T, H):
+    qkv = _bf16(B, T, 3 * H * 64, seed=2)
+    dout = _bf16(B, T, H * 64, seed=3)
+    out = torch.empty(B, T, H * 64, dtype=torch.bfloat16, device=DEV)
+    lse = torch.empty(B, H, T, device=DEV)
+    native.attention_fwd(qkv, out, lse, H)
+    dqkv = torch.empty_like(qkv)
+    scratch = torch.empty(native.attention_bwd_scratch_floats(B, T, H), device=DEV)
+    native.attention_bwd(qkv, out, dout, lse, dqkv, scratch, H)
+    qr = qkv.float().requires_grad_(True)
+    ref, _ = _attn_ref(qr, H)
+    ref.backward(dout.float())
+    scale = qr.grad.abs().max().item()
+    err = (dqkv.float() - qr.grad).abs().max().item()
+    assert err <= 0.03 * scale + 2e-2, f"max err {err} (grad scale {scale})"
