@@ -268,3 +268,96 @@ extern "C" int dtb_layernorm_bwd(const void* dy, const void* x, const void* gamm
   DTB_LAUNCH_OK();
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of dtb_layernorm_bwd.
+//
+// dtb_layernorm_bwd needs the caller to supply a scratch buffer for the per-chunk dgamma/dbeta
+// partial sums.  Some users of this C ABI have no way to produce one: a plain C or Fortran host
+// that links the library without a device allocator of its own, a plugin running inside a
+// framework that has already claimed the whole GPU and forbids cudaMalloc from guests, or a
+// latency-sensitive loop that cannot accept cudaMalloc's implicit device synchronisation and its
+// out-of-memory failure mode.  For them the scratch lives in the library image itself: a file-scope
+// __device__ array of DTB_LN_NOALLOC_MAX_COLS-sized capacity (32 chunks x 2 x 2048 floats = 512 KiB)
+// that every GPU which loads the library holds until the process exits.
+//
+// In host code the array's name is only a host-side handle, not a device address, so the address
+// the kernels receive is looked up with cudaGetSymbolAddress, once per device, with that device
+// current, on the first call made on that device.  Make that first call outside any stream capture.
+// The function calls no cudaMalloc / cudaFree or any other allocating routine.
+//
+// All calls on one GPU share the one array.  Nothing in it has to start at zero: every element the
+// finishing kernel reads is overwritten by the partial-sum kernel of the same call, so stale
+// contents from the previous call are harmless.  Two calls whose kernels overlap on the GPU (issued
+// to different streams without ordering between them) race on the array and give wrong dgamma /
+// dbeta; serialise them.
+// No counterpart in the reference.
+#include <mutex>
+
+namespace dtb {
+namespace ln {
+
+constexpr int NOALLOC_MAX_COLS = 2048;
+constexpr size_t NOALLOC_FLOATS = static_cast<size_t>(PARAM_CHUNKS) * 2 * NOALLOC_MAX_COLS;
+static __device__ __align__(256) float g_ln_noalloc_scratch[NOALLOC_FLOATS];
+
+// Device address of g_ln_noalloc_scratch on the current device (resolved once per device).
+static float* noalloc_scratch_ptr() {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float* resolved[kMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_error("dtb_layernorm_bwd_noalloc: cudaGetDevice failed or device index %d unsupported (%s)", dev,
+              cudaGetErrorString(e));
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (resolved[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_ln_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("dtb_layernorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    resolved[dev] = p;
+  }
+  return resolved[dev];
+}
+
+}  // namespace ln
+}  // namespace dtb
+
+extern "C" int dtb_layernorm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* mean,
+                                         const float* rstd, const void* dres_in, void* dx, float* dgamma,
+                                         float* dbeta, int rows, int cols, int accumulate_param_grads,
+                                         void* stream) {
+  DTB_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0, "dtb_layernorm_bwd_noalloc: cols=%d must be a positive multiple of 8",
+              cols);
+  DTB_REQUIRE(cols <= NOALLOC_MAX_COLS,
+              "dtb_layernorm_bwd_noalloc: cols=%d exceeds the built-in scratch capacity (max %d columns); use "
+              "dtb_layernorm_bwd with a caller-provided scratch buffer",
+              cols, NOALLOC_MAX_COLS);
+  float* scratch = noalloc_scratch_ptr();
+  if (scratch == nullptr) return 1;
+  int grid = (rows + WARPS - 1) / WARPS;
+  const int cap = sm_count() * 8;
+  if (grid > cap) grid = cap;
+  auto s = static_cast<cudaStream_t>(stream);
+  const int nv = (cols / 8 + 31) / 32;
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto G = static_cast<const __nv_bfloat16*>(gamma);
+  auto DR = static_cast<const __nv_bfloat16*>(dres_in);
+  auto DX = static_cast<__nv_bfloat16*>(dx);
+  if (nv <= 4) bwd_dx_kernel<4><<<grid, WARPS * 32, 0, s>>>(DY, X, G, mean, rstd, DR, DX, rows, cols);
+  else bwd_dx_kernel<8><<<grid, WARPS * 32, 0, s>>>(DY, X, G, mean, rstd, DR, DX, rows, cols);
+  DTB_LAUNCH_OK();
+  bwd_param_kernel<<<dim3((cols + 63) / 64, PARAM_CHUNKS), 256, 0, s>>>(DY, X, mean, rstd, scratch, rows, cols);
+  DTB_LAUNCH_OK();
+  bwd_finish_kernel<<<(2 * cols + 255) / 256, 256, 0, s>>>(scratch, PARAM_CHUNKS, cols, dgamma, dbeta,
+                                                           accumulate_param_grads);
+  DTB_LAUNCH_OK();
+  return 0;
+}

@@ -90,6 +90,20 @@ int dtb_layernorm_bwd(const void* dy, const void* x, const void* gamma, const fl
                       const void* dres_in, void* dx, float* dgamma, float* dbeta, float* scratch, int rows, int cols,
                       int accumulate_param_grads, void* stream);
 
+/* Same computation as dtb_layernorm_bwd, for callers that cannot hand over a scratch buffer because they
+ * cannot allocate device memory at all: a bare C/Fortran host with no device allocator, a plugin inside a
+ * framework that owns the whole GPU and forbids cudaMalloc, or a loop that cannot tolerate cudaMalloc's
+ * implicit synchronisation.  The scratch is a 512 KiB __device__ array inside the library (held by every GPU
+ * that loads it, until exit), which limits this entry point to cols <= DTB_LN_NOALLOC_MAX_COLS; larger
+ * rows are rejected with an error.  No allocating call is made.  The first call on each device resolves the
+ * array's device address (cudaGetSymbolAddress) — issue it outside stream capture.  All calls on a GPU share
+ * the array: calls whose kernels overlap on the GPU race; nothing needs zeroing between calls.
+ * No counterpart in the reference. */
+#define DTB_LN_NOALLOC_MAX_COLS 2048
+int dtb_layernorm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                              const void* dres_in, void* dx, float* dgamma, float* dbeta, int rows, int cols,
+                              int accumulate_param_grads, void* stream);
+
 /* ---- losses (K11/K12: F.cross_entropy / nn.MSELoss,
  *      /root/reference/src/distributed_trainer.py:163, playground/ddp_script.py:135) */
 /* Fused softmax cross-entropy with index targets: per-row loss (fp32) and, in place over
