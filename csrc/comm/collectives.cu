@@ -139,23 +139,74 @@ __global__ void __launch_bounds__(THREADS) barrier_kernel(const Ctx x) {
   store_seq(x, seq);
 }
 
+// Loads of U consecutive grid-strided vectors from all W ranks are issued before any is consumed:
+// U*W 16-byte requests per thread keep ~2-3 MB in flight per GPU, which is what NVLink's ~2 us
+// round trip needs to stream at full rate.
+template <int W>
+struct Unroll {
+  static constexpr int U = W >= 8 ? 2 : (W >= 4 ? 4 : 8);
+};
+
+struct SgdArgs {
+  size_t param_offset;   // params live in the heap with the same slot layout as the gradient bucket
+  float lr, decay;       // p = p * decay - lr * g   (decay = 1 - lr * weight_decay)
+};
+
 // Two-shot in-place mean.  nvec = number of 16-byte vectors in the buffer.
-template <bool FP32, int W>
-__global__ void __launch_bounds__(THREADS) allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec) {
+// SGD = true: instead of writing the mean gradient back, rank r applies the SGD update to slice r of the
+// parameters and stores the *new parameters* into every rank (gradient all-reduce + 1/W + optimizer step
+// in one pass over NVLink; bf16 only).
+template <bool FP32, int W, bool SGD>
+__global__ void __launch_bounds__(THREADS)
+allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec, const SgdArgs sgd) {
+  constexpr int U = Unroll<W>::U;
+  constexpr int N = Vec<FP32>::N;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);   // every rank's gradients are final
+  rank_barrier(x, seq);   // every rank's gradients are final (and, for SGD, nobody still reads the old params)
   const long long lo = nvec * x.c.rank / W, hi = nvec * (x.c.rank + 1) / W;
   const float scale = 1.f / W;
-  for (long long v = lo + static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < hi;
-       v += static_cast<long long>(gridDim.x) * THREADS) {
-    float acc[Vec<FP32>::N];
-    const size_t off = offset + static_cast<size_t>(v) * 16;
-    reduce_vec<FP32, W>(x, off, acc);
+  const long long stride = static_cast<long long>(gridDim.x) * THREADS;
+  for (long long v0 = lo + static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v0 < hi; v0 += stride * U) {
+    uint4 raw[U][W];
 #pragma unroll
-    for (int j = 0; j < Vec<FP32>::N; ++j) acc[j] *= scale;
-    const uint4 out = Vec<FP32>::pack(acc);
+    for (int u = 0; u < U; ++u) {
+      const long long v = v0 + u * stride;
+      if (v < hi) {
 #pragma unroll
-    for (int r = 0; r < W; ++r) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + off, out);
+        for (int r = 0; r < W; ++r)
+          raw[u][r] = ld_volatile_v4(static_cast<const uint8_t*>(x.c.peers[r]) + offset + static_cast<size_t>(v) * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= hi) break;
+      float acc[N];
+#pragma unroll
+      for (int j = 0; j < N; ++j) acc[j] = 0.f;
+#pragma unroll
+      for (int r = 0; r < W; ++r) {
+        float f[N];
+        Vec<FP32>::unpack(raw[u][r], f);
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] += f[j];
+      }
+      size_t dst = offset + static_cast<size_t>(v) * 16;
+      if (SGD) {
+        dst = sgd.param_offset + static_cast<size_t>(v) * 16;
+        const uint4 praw = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(x.c.peers[x.c.rank]) + dst);
+        float pf[N];
+        Vec<FP32>::unpack(praw, pf);
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] = pf[j] * sgd.decay - sgd.lr * (acc[j] * scale);
+      } else {
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] *= scale;
+      }
+      const uint4 out = Vec<FP32>::pack(acc);
+#pragma unroll
+      for (int r = 0; r < W; ++r) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + dst, out);
+    }
   }
   rank_barrier(x, seq);   // every slice has been delivered to this rank
   store_seq(x, seq);
@@ -372,11 +423,28 @@ extern "C" int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long lo
     });
   } else {
     const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 32);
+    const SgdArgs none = {0, 0.f, 1.f};
     DISPATCH_W(c->world, {
-      if (dtype == 1) allreduce_twoshot_kernel<true, W><<<grid, THREADS, 0, s>>>(x, offset, nvec);
-      else allreduce_twoshot_kernel<false, W><<<grid, THREADS, 0, s>>>(x, offset, nvec);
+      if (dtype == 1) allreduce_twoshot_kernel<true, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
+      else allreduce_twoshot_kernel<false, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
     });
   }
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, size_t param_offset, long long n,
+                                       float lr, float weight_decay, int max_ctas, void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  DTB_REQUIRE(grad_offset % 16 == 0 && param_offset % 16 == 0 && (n * 2) % 16 == 0,
+              "dtb_comm_all_reduce_sgd: buffers must be 16-byte granular");
+  if (n == 0) return 0;
+  Ctx x = {*c, channel_of(max_ctas)};
+  const long long nvec = n * 2 / 16;
+  const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 32);
+  const SgdArgs sgd = {param_offset, lr, 1.f - lr * weight_decay};
+  auto s = static_cast<cudaStream_t>(stream);
+  DISPATCH_W(c->world, { allreduce_twoshot_kernel<false, W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, sgd); });
   DTB_LAUNCH_OK();
   return 0;
 }

@@ -116,27 +116,46 @@ __global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16*
 }
 
 // Column sums of a row-major [rows, cols] bf16 matrix.  Each CTA owns 64 columns
-// (8 lanes x 8 columns) and 32 row-lanes; a shared-memory tree finishes the sum,
-// so no scratch buffer or atomics are needed and the result is deterministic.
-__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, void* __restrict__ out,
-                                                          int rows, int cols, long long ldx, int out_fp32) {
-  __shared__ float part[32][65];
+// (8 lanes x 8 columns) and 64 row-lanes, each row-lane keeps four independent 16-byte
+// loads in flight; a shared-memory tree finishes the sum, so no scratch buffer or
+// atomics are needed and the result is deterministic.
+constexpr int COLSUM_THREADS = 512;
+constexpr int COLSUM_ROWLANES = COLSUM_THREADS / 8;
+__global__ void __launch_bounds__(COLSUM_THREADS) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                     void* __restrict__ out, int rows, int cols,
+                                                                     long long ldx, int out_fp32) {
+  __shared__ float part[COLSUM_ROWLANES][65];
   const int cx = threadIdx.x & 7;    // column group within the CTA
-  const int ry = threadIdx.x >> 3;   // 0..31 row lane
+  const int ry = threadIdx.x >> 3;   // row lane
   const int col = blockIdx.x * 64 + cx * 8;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (col < cols) {
-    const bool vec = (col + 8 <= cols);
-    for (int r = ry; r < rows; r += 32) {
-      const __nv_bfloat16* p = x + static_cast<long long>(r) * ldx + col;
-      if (vec) {
+    if (col + 8 <= cols) {
+      int r = ry;
+      for (; r + 3 * COLSUM_ROWLANES < rows; r += 4 * COLSUM_ROWLANES) {
+        Bf16x8 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          v[u].raw = *reinterpret_cast<const uint4*>(x + static_cast<long long>(r + u * COLSUM_ROWLANES) * ldx + col);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float f[8];
+          v[u].unpack(f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+      }
+      for (; r < rows; r += COLSUM_ROWLANES) {
         Bf16x8 v;
-        v.raw = *reinterpret_cast<const uint4*>(p);
+        v.raw = *reinterpret_cast<const uint4*>(x + static_cast<long long>(r) * ldx + col);
         float f[8];
         v.unpack(f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] += f[j];
-      } else {
+      }
+    } else {
+      for (int r = ry; r < rows; r += COLSUM_ROWLANES) {
+        const __nv_bfloat16* p = x + static_cast<long long>(r) * ldx + col;
         for (int j = 0; j < 8 && col + j < cols; ++j) acc[j] += __bfloat162float(p[j]);
       }
     }
@@ -147,7 +166,7 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
   if (threadIdx.x < 64) {
     float s = 0.f;
 #pragma unroll 8
-    for (int r = 0; r < 32; ++r) s += part[r][threadIdx.x];
+    for (int r = 0; r < COLSUM_ROWLANES; ++r) s += part[r][threadIdx.x];
     const int c = blockIdx.x * 64 + threadIdx.x;
     if (c < cols) {
       if (out_fp32) reinterpret_cast<float*>(out)[c] = s;
@@ -249,7 +268,7 @@ extern "C" int dtb_colsum_bf16(const void* x, void* out, int rows, int cols, lon
                                void* stream) {
   DTB_REQUIRE(rows > 0 && cols > 0, "dtb_colsum_bf16: empty input");
   DTB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "dtb_colsum_bf16: x must be 16-byte aligned");
-  colsum_bf16_kernel<<<(cols + 63) / 64, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  colsum_bf16_kernel<<<(cols + 63) / 64, COLSUM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), out, rows, cols, ldx, out_fp32);
   DTB_LAUNCH_OK();
   return 0;

@@ -52,7 +52,7 @@ struct Config {
   static constexpr int B_ROWS = BN / CG;                   // B rows staged by one CTA
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (STAGE_BYTES >= 48 * 1024) ? 4 : 6;
+  static constexpr int STAGES = (STAGE_BYTES >= 48 * 1024) ? 4 : 7;
   static constexpr int TMEM_COLS = 2 * BN;                 // two accumulator stages
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
   static_assert(TMEM_COLS <= 512, "TMEM has 512 columns");
@@ -260,20 +260,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
 
   if (warp == 0) {
     // ============================ TMA producer ============================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        int bi, m_blk, n_blk;
-        tile_coords(p, tile, bi, m_blk, n_blk);
-        const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
-        const int m0 = (m_blk * CG + static_cast<int>(cta_rank)) * BM;
-        const int n0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
-          uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
-          const int k0 = kb * BK;
+    // The whole warp walks the loop so every address / coordinate stays in uniform registers;
+    // one elected lane issues the copies (a lane-0-only region makes ptxas wrap each UTMALDG
+    // in a vote / R2UR waterfall).
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int bi, m_blk, n_blk;
+      tile_coords(p, tile, bi, m_blk, n_blk);
+      const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
+      const int m0 = (m_blk * CG + static_cast<int>(cta_rank)) * BM;
+      const int n0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
+        uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
+        const int k0 = kb * BK;
+        if (elect_one()) {
           if (CG == 1 || leader) mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES * CG);
           if constexpr (CG == 1) {
             if constexpr (A_MN) {
@@ -306,21 +309,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
               tma_load_4d_2sm(sb, &map_b, &full_bar[stage], k0, n0, b_in, b_out);
             }
           }
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
         }
       }
     }
   } else if (warp == 1) {
     // ============================= MMA issuer =============================
-    if (lane == 0 && leader) {
+    if (leader) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM * CG, BN, A_MN, B_MN);
-      // bytes to advance the descriptor start address per UMMA_K (16 elements of K):
-      //   K-major: 32 bytes inside the 128-byte swizzled row; MN-major: two 8-row groups of 128 B rows
-      constexpr uint32_t A_KSTEP = A_MN ? 2048u : 32u;
-      constexpr uint32_t B_KSTEP = B_MN ? 2048u : 32u;
+      // Descriptor start-address advance per UMMA_K (16 elements of K), in 16-byte units:
+      //   K-major: 32 B inside the 128-byte swizzled row; MN-major: two 8-row groups of 128 B rows.
+      constexpr uint32_t A_KSTEP16 = (A_MN ? 2048u : 32u) >> 4;
+      constexpr uint32_t B_KSTEP16 = (B_MN ? 2048u : 32u) >> 4;
+      // Descriptor halves that do not change inside the loop: hi = SBO | version 1 | 128B swizzle,
+      // lo = start address (>>4) | LBO.  Stage bases differ by a constant, K steps by an immediate.
+      const uint32_t a_hi = ((p.sbo_a >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+      const uint32_t b_hi = ((p.sbo_b >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+      const uint32_t a_lo0 = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (((p.lbo_a >> 4) & 0x3FFFu) << 16);
+      const uint32_t b_lo0 = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | (((p.lbo_b >> 4) & 0x3FFFu) << 16);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -332,28 +342,33 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tcgen05_fence_after();
-          const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES);
-          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::B_BYTES);
+          const uint32_t a_lo = a_lo0 + static_cast<uint32_t>(stage) * (Cfg::A_BYTES >> 4);
+          const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(stage) * (Cfg::B_BYTES >> 4);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t da = umma_smem_desc(a_addr + k * A_KSTEP, p.lbo_a, p.sbo_a);
-            const uint64_t db = umma_smem_desc(b_addr + k * B_KSTEP, p.lbo_b, p.sbo_b);
-            umma_f16<CG>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t da = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * A_KSTEP16);
+              const uint64_t db = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * B_KSTEP16);
+              umma_f16<CG>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            if constexpr (CG == 1) {
+              umma_commit(&empty_bar[stage]);
+            } else {
+              umma_commit_2sm(&empty_bar[stage], 0x3);
+            }
+            if (kb == num_kb - 1) {
+              if constexpr (CG == 1) {
+                umma_commit(&tmem_full[acc]);
+              } else {
+                umma_commit_2sm(&tmem_full[acc], 0x3);
+              }
+            }
           }
-          if constexpr (CG == 1) {
-            umma_commit(&empty_bar[stage]);
-          } else {
-            umma_commit_2sm(&empty_bar[stage], 0x3);
-          }
+          __syncwarp();
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
-        }
-        if constexpr (CG == 1) {
-          umma_commit(&tmem_full[acc]);
-        } else {
-          umma_commit_2sm(&tmem_full[acc], 0x3);
         }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;

@@ -75,11 +75,15 @@ class MLP(nn.Module):
         return ws
 
     def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, loss: str = "cross_entropy",
-                         grad_sink: Any = None, max_ctas: int = 0) -> torch.Tensor:
+                         grad_sink: Any = None, max_ctas: int = 0,
+                         fused_sgd: Optional[Tuple[float, float]] = None, on_updated: Any = None) -> torch.Tensor:
         """Fused training step (no autograd).  Returns the mean loss (0-dim fp32 tensor).
 
         ``grad_sink`` (a ``ReplicatedModule``) supplies ``grad_view(param)`` and
         ``mark_ready(param)``; without one, gradients land in ``param.grad``.
+        ``fused_sgd=(lr, weight_decay)`` makes the wgrad GEMM epilogue apply the SGD update to the
+        weight in place (single replica only); ``on_updated(params)`` is told which parameters were
+        stepped that way so the optimizer skips them.
         """
         if loss != "cross_entropy" or targets.dtype != torch.int64:
             raise NotImplementedError("native MLP step supports cross_entropy with int64 class targets")
@@ -115,20 +119,32 @@ class MLP(nn.Module):
             layer = self.layers[i]
             out_f, in_f = layer.weight.shape
             h_in = x if i == 0 else ws["h"][i - 1]
-            # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major)
-            native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
-                        lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
+            nxt = None
+            if i > 0:
+                # dgrad fused with GELU': dz_prev = (dz W_i) * gelu'(z_{i-1}).  It runs BEFORE this layer's
+                # wgrad is handed to the reducer: a fused reduce+SGD (or the fused epilogue below) overwrites W_i.
+                nxt = ws["dz"][i % 2]
+                native.gemm(dz, layer.weight, nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
+                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=max_ctas)
+            if fused_sgd is not None:
+                # single replica: W = (1 - lr*wd) W - lr * (dz^T h_in), applied in the wgrad epilogue (no dW in HBM)
+                lr, wd = fused_sgd
+                native.gemm(dz, h_in, layer.weight.data, m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
+                            lda=dz.shape[1], ldb=in_f, aux=layer.weight.data, alpha=-lr, beta=1.0 - lr * wd,
+                            max_ctas=max_ctas)
+                if on_updated is not None:
+                    on_updated([layer.weight])
+            else:
+                # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major), straight into the gradient bucket
+                native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
+                            lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
             if layer.bias is not None:
                 native.colsum(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
             if grad_sink is not None:
                 grad_sink.mark_ready(layer.weight)
                 if layer.bias is not None:
                     grad_sink.mark_ready(layer.bias)
-            if i > 0:
-                # dgrad fused with GELU': dz_prev = (dz W_i) * gelu'(z_{i-1})
-                nxt = ws["dz"][i % 2]
-                native.gemm(dz, layer.weight, nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
-                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=max_ctas)
+            if nxt is not None:
                 dz = nxt
         return ws["loss"]
 

@@ -373,6 +373,13 @@ def comm_all_reduce_avg(desc: CommDesc, offset: int, numel: int, fp32: bool, alg
                                       _cta_arg(max_ctas, channel), _stream()))
 
 
+def comm_all_reduce_sgd(desc: CommDesc, grad_offset: int, param_offset: int, numel: int, lr: float,
+                        weight_decay: float, max_ctas: int = 0, channel: int = 0):
+    _ok(lib().dtb_comm_all_reduce_sgd(C.byref(desc), C.c_size_t(grad_offset), C.c_size_t(param_offset),
+                                      C.c_longlong(numel), C.c_float(lr), C.c_float(weight_decay),
+                                      _cta_arg(max_ctas, channel), _stream()))
+
+
 def comm_all_gather(desc: CommDesc, dst_offset: int, src_offset: int, numel: int, esize: int, max_ctas: int = 0,
                     channel: int = 0):
     _ok(lib().dtb_comm_all_gather(C.byref(desc), C.c_size_t(dst_offset), C.c_size_t(src_offset), C.c_longlong(numel),

@@ -33,6 +33,15 @@ class _FusedBase(torch.optim.Optimizer):
         super().__init__(params, defaults)
         self.master_weights = master_weights
         self._step_count = 0
+        self._already_updated: set = set()
+
+    def mark_updated(self, params) -> None:
+        """Parameters whose update for the current step was applied by a fused kernel (gradient
+        all-reduce + SGD, or the wgrad GEMM epilogue); the next ``step()`` leaves them alone."""
+        self._already_updated.update(id(p) for p in params)
+
+    def _pending(self, group) -> List[torch.Tensor]:
+        return [p for p in group["params"] if p.grad is not None and id(p) not in self._already_updated]
 
     def zero_grad(self, set_to_none: bool = False) -> None:  # keep bucket views attached
         if set_to_none:
@@ -57,6 +66,11 @@ class FusedSGD(_FusedBase):
                  master_weights: bool = False) -> None:
         super().__init__(params, dict(lr=lr, momentum=momentum, weight_decay=weight_decay), master_weights)
 
+    @property
+    def fusable_sgd(self) -> bool:
+        """Stateless update (no momentum, no master copy): can be folded into a reduction / GEMM epilogue."""
+        return not self.master_weights and all(g["momentum"] == 0.0 for g in self.param_groups)
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
@@ -64,7 +78,7 @@ class FusedSGD(_FusedBase):
         native = _native()
         for group in self.param_groups:
             lr, mom, wd = group["lr"], group["momentum"], group["weight_decay"]
-            params = [p for p in group["params"] if p.grad is not None]
+            params = self._pending(group)
             if not params:
                 continue
             grads = [p.grad for p in params]
@@ -99,6 +113,7 @@ class FusedSGD(_FusedBase):
             for p, t in zip(params, targets):
                 if t is not p:
                     p.copy_(t)
+        self._already_updated.clear()
         return loss
 
 

@@ -46,6 +46,7 @@ class GradBucket:
     def __init__(self, plan: BucketPlan, buffer: torch.Tensor, params: List[nn.Parameter]) -> None:
         self.plan = plan
         self.buffer = buffer
+        self.param_buffer: Optional[torch.Tensor] = None     # parameters with the same slot layout (fused step)
         self.views: Dict[int, torch.Tensor] = {}
         for slot in plan.slots:
             self.views[slot.param_index] = buffer[slot.offset: slot.offset + slot.numel].view(slot.shape)
@@ -84,14 +85,26 @@ class ReplicatedModule(nn.Module):
 
         plans = plan_buckets(self._params, int(bucket_cap_mb * (1 << 20)),
                              int(first_bucket_mb * (1 << 20)), reverse=True, grad_dtype=grad_dtype)
-        comm.reserve(sum(pl.nbytes + 256 for pl in plans))
+        # On the peer-memory communicator the parameters themselves are re-homed into the heap, laid out
+        # like their gradient bucket, so a bucket's reduction can be fused with the optimizer step.
+        self.params_in_heap = bool(getattr(comm, "supports_fused_step", False)) and grad_dtype is None
+        comm.reserve(sum(pl.nbytes + 256 for pl in plans) * (2 if self.params_in_heap else 1))
         self.buckets: List[GradBucket] = []
         self._bucket_of: Dict[int, GradBucket] = {}
         for plan in plans:
             bucket = GradBucket(plan, comm.alloc(plan.numel, plan.dtype), self._params)
+            if self.params_in_heap:
+                bucket.param_buffer = comm.alloc(plan.numel, plan.dtype)
+                with torch.no_grad():
+                    for slot in plan.slots:
+                        p = self._params[slot.param_index]
+                        home = bucket.param_buffer[slot.offset: slot.offset + slot.numel].view(slot.shape)
+                        home.copy_(p.data)
+                        p.data = home
             self.buckets.append(bucket)
             for idx in plan.param_indices:
                 self._bucket_of[idx] = bucket
+        self._optimizer: Any = None
         self._hook_handles = []
         for i, p in enumerate(self._params):
             self._hook_handles.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
@@ -159,9 +172,27 @@ class ReplicatedModule(nn.Module):
         if bucket.pending == 0:
             self._launch(bucket)
 
+    # ------------------------------------------------------------- fused step
+    def attach_optimizer(self, optimizer: Any) -> None:
+        """Let gradient reduction and the optimizer step run as one kernel where that is exact:
+        plain SGD (no momentum, no master weights) on bf16 parameters of a native-step model."""
+        self._optimizer = optimizer
+
+    def _fused_sgd_hyper(self) -> Optional[Tuple[float, float]]:
+        opt = self._optimizer
+        if opt is None or not getattr(opt, "fusable_sgd", False) or not self.params_in_heap or not self.native_step:
+            return None
+        group = opt.param_groups[0]
+        return float(group["lr"]), float(group["weight_decay"])
+
     def _launch(self, bucket: GradBucket) -> None:
         if self.comm.world_size > 1:      # a single replica already holds the mean
-            bucket.work = self.comm.all_reduce_avg_(bucket.buffer)
+            hyper = self._fused_sgd_hyper() if self._in_manual_step else None
+            if hyper is not None and bucket.param_buffer is not None and bucket.plan.dtype == torch.bfloat16:
+                bucket.work = self.comm.all_reduce_sgd_(bucket.buffer, bucket.param_buffer, *hyper)
+                self._optimizer.mark_updated(self._params[i] for i in bucket.plan.param_indices)
+            else:
+                bucket.work = self.comm.all_reduce_avg_(bucket.buffer)
         bucket.launched = True
 
     def _finalize_backward(self) -> None:
@@ -187,10 +218,15 @@ class ReplicatedModule(nn.Module):
             raise AttributeError(f"{type(self.module).__name__} has no native forward_backward")
         self._in_manual_step = True
         try:
+            hyper = self._fused_sgd_hyper()
+            if hyper is not None and self.comm.world_size == 1:
+                # single replica: the wgrad GEMM epilogue applies W -= lr*(dW + wd*W) itself
+                kwargs["fused_sgd"] = hyper
+                kwargs["on_updated"] = self._optimizer.mark_updated
             loss = self.module.forward_backward(inputs, targets, grad_sink=self, **kwargs)
+            self.finish_gradient_sync()
         finally:
             self._in_manual_step = False
-        self.finish_gradient_sync()
         return loss
 
     def finish_gradient_sync(self) -> None:

@@ -71,6 +71,9 @@ class _StreamWork(Work):
 class SymmComm(Communicator):
     """Peer-memory communicator; one per process (one process per GPU)."""
 
+    #: parameters may be re-homed into the heap so reduction + optimizer step fuse (``all_reduce_sgd_``)
+    supports_fused_step = True
+
     def __init__(self, device: torch.device, segment_bytes: int = DEFAULT_SEGMENT_BYTES,
                  comm_ctas: int = 0, overlap_stream: bool = True) -> None:
         native.require()
@@ -217,6 +220,22 @@ class SymmComm(Communicator):
         numel = (buf.numel() * esize + 15) // 16 * 16 // esize      # heap slots are padded to 256 B
         with self._on_comm_stream():
             native.comm_all_reduce_avg(seg.desc, off, numel, buf.dtype == torch.float32, 0, self.comm_ctas)
+            event = torch.cuda.Event()
+            event.record()
+        return _StreamWork(event)
+
+    def all_reduce_sgd_(self, grads: torch.Tensor, params: torch.Tensor, lr: float, weight_decay: float) -> Work:
+        """Average ``grads`` over ranks and apply ``p = p*(1-lr*wd) - lr*g`` to ``params`` (same layout, both in
+        the same heap segment) in one kernel; every rank ends with identical new parameters."""
+        if grads.dtype != torch.bfloat16 or params.dtype != torch.bfloat16:
+            raise TypeError("all_reduce_sgd_ is a bf16 path")
+        seg, g_off = self.locate(grads)
+        seg_p, p_off = self.locate(params)
+        if seg is not seg_p:
+            raise ValueError("all_reduce_sgd_: grads and params must live in the same symmetric segment")
+        numel = (grads.numel() * 2 + 15) // 16 * 8
+        with self._on_comm_stream():
+            native.comm_all_reduce_sgd(seg.desc, g_off, p_off, numel, lr, weight_decay, self.comm_ctas)
             event = torch.cuda.Event()
             event.record()
         return _StreamWork(event)

@@ -243,8 +243,12 @@ class Trainer:
             optimizer = OptimizerSpec(self.config.optimizer, lr=self.config.learning_rate,
                                       weight_decay=self.config.weight_decay)
         if isinstance(optimizer, OptimizerSpec):
-            return self._strategy.build_optimizer(self.model, optimizer)
-        return self._strategy.adopt_optimizer(self.model, optimizer)
+            optimizer = self._strategy.build_optimizer(self.model, optimizer)
+        else:
+            optimizer = self._strategy.adopt_optimizer(self.model, optimizer)
+        if hasattr(self.model, "attach_optimizer"):
+            self.model.attach_optimizer(optimizer)
+        return optimizer
 
     # ------------------------------------------------------------------- steps
     def _loss(self, output: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
@@ -255,10 +259,11 @@ class Trainer:
         return F.cross_entropy(output.float(), targets.float())
 
     def _run_batch(self, source: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
-        self.optimizer.zero_grad()
         if getattr(self.model, "native_step", False):
+            # native kernels overwrite their gradient buffers: no zero_grad pass over the parameters
             loss = self.model.forward_backward(source, targets, loss=self.config.loss)
         else:
+            self.optimizer.zero_grad()
             output = self.model(source)
             loss = self._loss(output, targets)
             loss.backward()

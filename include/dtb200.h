@@ -180,6 +180,11 @@ int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes, int root,
  * 2 two-shot, 3 NVLS multimem */
 int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long long n, int dtype, int algo, int max_ctas,
                             void* stream);
+/* Gradient all-reduce fused with the optimizer step (bf16): rank r averages slice r of the gradients over
+ * all ranks, applies p = p*(1 - lr*wd) - lr*g to slice r of the parameters (same layout at param_offset)
+ * and stores the NEW PARAMETERS into every rank.  The gradient buffers are left untouched. */
+int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, size_t param_offset, long long n, float lr,
+                            float weight_decay, int max_ctas, void* stream);
 /* dst[r*n .. (r+1)*n) = rank r's src[0..n)  (element size esize) */
 int dtb_comm_all_gather(const dtb_comm* c, size_t dst_offset, size_t src_offset, long long n, int esize,
                         int max_ctas, void* stream);

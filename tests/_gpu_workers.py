@@ -92,22 +92,25 @@ def ddp_native(rank, world, port, out_dir):
     _init(rank, world, port)
     strategy = DDPStrategy(rank, True)
     try:
+      for fused in (False, True):
         torch.manual_seed(100 + rank)                        # rank-dependent init: must be broadcast
         model = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16).cuda()
         wrapped = strategy.prepare_model(model, rank)
         assert wrapped.native_step
-        opt = strategy.build_optimizer(wrapped, OptimizerSpec("sgd", lr=0.05))
+        opt = strategy.build_optimizer(wrapped, OptimizerSpec("sgd", lr=0.05, weight_decay=0.01))
+        if fused:
+            wrapped.attach_optimizer(opt)                    # gradient all-reduce + SGD in one kernel
+            assert wrapped._fused_sgd_hyper() is not None
         torch.manual_seed(100)
         ref = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16)
         ref = ref.float().cuda()
         for (k1, v1), (k2, v2) in zip(wrapped.state_dict().items(), ref.state_dict().items()):
             assert k1 == "module." + k2 and torch.equal(v1.float(), v2), k1
-        ropt = torch.optim.SGD(ref.parameters(), lr=0.05)
+        ropt = torch.optim.SGD(ref.parameters(), lr=0.05, weight_decay=0.01)
         g = torch.Generator().manual_seed(9)
         for step in range(4):
             x = torch.randn(world * 128, 256, generator=g).to(torch.bfloat16).cuda()
             y = torch.randint(0, 384, (world * 128,), generator=g).cuda()
-            opt.zero_grad()
             loss = wrapped.forward_backward(x[rank * 128:(rank + 1) * 128], y[rank * 128:(rank + 1) * 128])
             opt.step()
             ropt.zero_grad()
@@ -116,7 +119,7 @@ def ddp_native(rank, world, port, out_dir):
             ropt.step()
         torch.cuda.synchronize()
         for (k, v), (_, rv) in zip(model.state_dict().items(), ref.state_dict().items()):
-            assert torch.allclose(v.float(), rv, atol=3e-2, rtol=3e-2), (k, (v.float() - rv).abs().max())
+            assert torch.allclose(v.float(), rv, atol=3e-2, rtol=3e-2), (fused, k, (v.float() - rv).abs().max())
         flat = torch.cat([p.detach().float().view(-1) for p in model.parameters()])
         got = _gather_cpu(flat, world)
         assert all(torch.equal(got[0], t) for t in got), "replicas diverged"

@@ -345,3 +345,31 @@ def test_attention_bwd(B, T, H):
     scale = qr.grad.abs().max().item()
     err = (dqkv.float() - qr.grad).abs().max().item()
     assert err <= 0.03 * scale + 2e-2, f"max err {err} (grad scale {scale})"
+
+
+def test_single_gpu_fused_sgd_in_wgrad_epilogue_matches_reference():
+    """World size 1: the wgrad GEMM epilogue applies the SGD update; weights must track an fp32 autograd run."""
+    from distributed_training_b200.models.mlp import MLP
+    from distributed_training_b200.parallel.ddp import DDPStrategy
+    from distributed_training_b200.parallel.strategy import OptimizerSpec
+
+    torch.manual_seed(0)
+    model = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16).to(DEV)
+    ref = MLP(256, 512, 384, num_layers=3, dtype=torch.float32).to(DEV)
+    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    strategy = DDPStrategy(0, True)
+    wrapped = strategy.prepare_model(model, 0)
+    opt = strategy.build_optimizer(wrapped, OptimizerSpec("sgd", lr=0.05, weight_decay=0.01))
+    wrapped.attach_optimizer(opt)
+    assert wrapped._fused_sgd_hyper() is not None and wrapped.comm.world_size == 1
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05, weight_decay=0.01)
+    for step in range(4):
+        x, y = _bf16(192, 256, seed=step), torch.randint(0, 384, (192,), device=DEV)
+        wrapped.forward_backward(x, y)
+        opt.step()
+        ropt.zero_grad()
+        F.cross_entropy(ref(x.float()), y).backward()
+        ropt.step()
+    for (k, v), (_, rv) in zip(model.state_dict().items(), ref.state_dict().items()):
+        assert torch.allclose(v.float(), rv, atol=3e-2, rtol=3e-2), (k, (v.float() - rv).abs().max())
+    strategy.comm.close()
