@@ -35,7 +35,8 @@ namespace comm {
 
 constexpr int MAX_BLOCKS = 64;       // barrier slots per channel
 constexpr int NUM_CHANNELS = 16;
-constexpr int THREADS = 512;
+constexpr int THREADS = 256;      // 256 threads x <= 80 registers: a comm CTA fits on an SM NEXT TO a resident GEMM CTA
+constexpr int MIN_CTAS_PER_SM = 3; // launch-bounds hint that caps registers at 65536 / (256 * 3) = 85 -> 80
 // signal pad layout (uint32 slots)
 constexpr int FLAG_SLOTS = NUM_CHANNELS * MAX_BLOCKS * DTB_MAX_RANKS;   // 8192
 constexpr int SEQ_BASE = FLAG_SLOTS;                                     // [channel][block] next sequence
@@ -133,18 +134,18 @@ __device__ __forceinline__ void reduce_vec(const Ctx& x, size_t byte_off, float*
 }
 
 // ---- kernels ------------------------------------------------------------------
-__global__ void __launch_bounds__(THREADS) barrier_kernel(const Ctx x) {
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) barrier_kernel(const Ctx x) {
   uint32_t seq = load_seq(x);
   rank_barrier(x, seq);
   store_seq(x, seq);
 }
 
 // Loads of U consecutive grid-strided vectors from all W ranks are issued before any is consumed:
-// U*W 16-byte requests per thread keep ~2-3 MB in flight per GPU, which is what NVLink's ~2 us
+// U*W = 8 16-byte requests per thread x 64 CTAs x 256 threads keep ~2 MB in flight per GPU, what NVLink's ~2 us
 // round trip needs to stream at full rate.
 template <int W>
 struct Unroll {
-  static constexpr int U = W >= 8 ? 2 : (W >= 4 ? 4 : 8);
+  static constexpr int U = W >= 8 ? 1 : (W >= 4 ? 2 : 4);
 };
 
 struct SgdArgs {
@@ -157,7 +158,7 @@ struct SgdArgs {
 // parameters and stores the *new parameters* into every rank (gradient all-reduce + 1/W + optimizer step
 // in one pass over NVLink; bf16 only).
 template <bool FP32, int W, bool SGD>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
 allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec, const SgdArgs sgd) {
   constexpr int U = Unroll<W>::U;
   constexpr int N = Vec<FP32>::N;
@@ -215,7 +216,7 @@ allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec, const SgdAr
 // One-shot in-place mean for small buffers: each rank reduces the whole buffer into
 // registers, all ranks meet (nobody may overwrite data a peer still reads), then store.
 template <bool FP32, int W, int PER_THREAD>
-__global__ void __launch_bounds__(THREADS) allreduce_oneshot_kernel(const Ctx x, size_t offset, long long nvec) {
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allreduce_oneshot_kernel(const Ctx x, size_t offset, long long nvec) {
   uint32_t seq = load_seq(x);
   rank_barrier(x, seq);
   float acc[PER_THREAD][Vec<FP32>::N];
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(THREADS) allreduce_oneshot_kernel(const Ctx x,
   store_seq(x, seq);
 }
 
-__global__ void __launch_bounds__(THREADS) broadcast_kernel(const Ctx x, size_t offset, long long nvec, int root) {
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) broadcast_kernel(const Ctx x, size_t offset, long long nvec, int root) {
   uint32_t seq = load_seq(x);
   rank_barrier(x, seq);   // destinations are free to be overwritten
   if (x.c.rank == root) {
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(THREADS) broadcast_kernel(const Ctx x, size_t 
 }
 
 // Push all-gather: rank r stores its shard (nvec vectors at src_off) to dst_off + r*shard on every rank.
-__global__ void __launch_bounds__(THREADS) allgather_kernel(const Ctx x, size_t dst_off, size_t src_off, long long nvec) {
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allgather_kernel(const Ctx x, size_t dst_off, size_t src_off, long long nvec) {
   uint32_t seq = load_seq(x);
   rank_barrier(x, seq);
   const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[x.c.rank]) + src_off;
@@ -279,7 +280,7 @@ struct OptArgs {
 
 // Reduce-scatter (mean) of slice `rank`; MODE 0: write fp32/bf16 result to `out`; MODE 1: fused optimizer.
 template <bool FP32, int W, int MODE>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
 reduce_scatter_kernel(const Ctx x, size_t src_off, long long nvec, void* out, int out_fp32, const OptArgs o) {
   uint32_t seq = load_seq(x);
   rank_barrier(x, seq);
@@ -393,7 +394,7 @@ extern "C" int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes
   if (bytes == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = static_cast<long long>(bytes / 16);
-  broadcast_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 32), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, offset, nvec,
+  broadcast_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 64), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, offset, nvec,
                                                                                                         root);
   DTB_LAUNCH_OK();
   return 0;
@@ -422,7 +423,7 @@ extern "C" int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long lo
       else allreduce_oneshot_kernel<false, W, PT><<<static_cast<int>(blocks), THREADS, 0, s>>>(x, offset, nvec);
     });
   } else {
-    const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 32);
+    const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 64);
     const SgdArgs none = {0, 0.f, 1.f};
     DISPATCH_W(c->world, {
       if (dtype == 1) allreduce_twoshot_kernel<true, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
@@ -441,7 +442,7 @@ extern "C" int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, si
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * 2 / 16;
-  const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 32);
+  const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 64);
   const SgdArgs sgd = {param_offset, lr, 1.f - lr * weight_decay};
   auto s = static_cast<cudaStream_t>(stream);
   DISPATCH_W(c->world, { allreduce_twoshot_kernel<false, W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, sgd); });
@@ -457,7 +458,7 @@ extern "C" int dtb_comm_all_gather(const dtb_comm* c, size_t dst_offset, size_t 
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * esize / 16;
-  allgather_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 32), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  allgather_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 64), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       x, dst_offset, src_offset, nvec);
   DTB_LAUNCH_OK();
   return 0;
@@ -471,7 +472,7 @@ extern "C" int dtb_comm_reduce_scatter_avg(const dtb_comm* c, void* out, int out
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * esize / 16;
-  const int grid = pick_grid(nvec, ctas_of(max_ctas), 32);
+  const int grid = pick_grid(nvec, ctas_of(max_ctas), 64);
   auto s = static_cast<cudaStream_t>(stream);
   OptArgs o = {};
   DISPATCH_W(c->world, {
@@ -493,7 +494,7 @@ extern "C" int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t s
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * 2 / 16;
-  const int grid = pick_grid(nvec, ctas_of(max_ctas), 32);
+  const int grid = pick_grid(nvec, ctas_of(max_ctas), 64);
   OptArgs o = {master, m, v,
                reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(c->peers[c->rank]) + shard_offset),
                opt, lr, beta1, beta2, eps, weight_decay, bias_corr1, bias_corr2, momentum};
