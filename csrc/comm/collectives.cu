@@ -33,8 +33,8 @@
 namespace dtb {
 namespace comm {
 
-constexpr int MAX_BLOCKS = 64;       // barrier slots per channel
-constexpr int NUM_CHANNELS = 16;
+constexpr int MAX_BLOCKS = 128;      // barrier slots per channel
+constexpr int NUM_CHANNELS = 8;
 constexpr int THREADS = 256;      // 256 threads x <= 80 registers: a comm CTA fits on an SM NEXT TO a resident GEMM CTA
 constexpr int MIN_CTAS_PER_SM = 3; // launch-bounds hint that caps registers at 65536 / (256 * 3) = 85 -> 80
 // signal pad layout (uint32 slots)

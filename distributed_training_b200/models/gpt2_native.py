@@ -1,0 +1,160 @@
+"""Hand-scheduled GPT-2 training step on the sm_100a kernels (no autograd).
+
+Forward, per block (residual stream ``x``; every matmul is ``native.gemm``):
+
+    a    = LN1(x)                                   layernorm_fwd
+    qkv  = a Wqkv^T + b                             GEMM + bias epilogue
+    att  = causal_attention(qkv)                    tcgen05 flash attention (S/P never leave the SM)
+    xm   = x + att Wo^T + bo                        GEMM + bias + residual epilogue
+    m    = LN2(xm)
+    h    = gelu(m Wfc^T + bfc)   (z kept)           GEMM + bias + GELU epilogue, pre-activation as 2nd output
+    x'   = xm + h Wpr^T + bpr                       GEMM + bias + residual epilogue
+
+then ``LN_f``, the tied LM head GEMM over the padded vocabulary and the fused softmax-CE kernel that
+overwrites the logits with their gradient.  Backward walks the same graph in reverse: each Linear is
+a dgrad GEMM (GELU' fused where a GELU preceded) followed by a wgrad GEMM that writes straight into
+the caller's gradient bucket, bias gradients are column sums, LayerNorm backward folds the residual
+branch's gradient in.  A weight's dgrad is always queued before its wgrad is handed to the reducer
+(``grad_sink.mark_ready``), because a fused reduce+optimizer kernel may overwrite the weight.
+
+The reference has no transformer; the baseline for this path is eager PyTorch + SDPA.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional
+
+import torch
+from torch import nn
+
+from ..ops import native
+
+
+def _workspace(model, B: int, T: int, device: torch.device) -> Dict[str, Any]:
+    key = (B, T, device)
+    ws = model._ws.get(key)
+    if ws is not None:
+        return ws
+    cfg = model.cfg
+    C, H, V, L = cfg.n_embd, cfg.n_head, cfg.padded_vocab, cfg.n_layer
+    R = B * T
+    bf = dict(dtype=torch.bfloat16, device=device)
+    f32 = dict(dtype=torch.float32, device=device)
+
+    def act(cols):
+        return torch.empty(R, cols, **bf)
+
+    blocks = []
+    for _ in range(L):
+        blocks.append({
+            "a": act(C), "qkv": torch.empty(B, T, 3 * C, **bf), "att": act(C), "xm": act(C), "m": act(C),
+            "z": act(4 * C), "h": act(4 * C), "x_out": act(C),
+            "lse": torch.empty(B, H, T, **f32),
+            "mean1": torch.empty(R, **f32), "rstd1": torch.empty(R, **f32),
+            "mean2": torch.empty(R, **f32), "rstd2": torch.empty(R, **f32),
+        })
+    ws = {
+        "blocks": blocks,
+        "x0": act(C), "xf": act(C), "meanf": torch.empty(R, **f32), "rstdf": torch.empty(R, **f32),
+        "logits": torch.empty(R, V, **bf),
+        "row_loss": torch.empty(R, **f32), "loss": torch.empty((), **f32),
+        # backward temporaries (reused by every block)
+        "dx": [act(C), act(C)], "dC": act(C), "d4C": act(4 * C), "dqkv": torch.empty(B, T, 3 * C, **bf),
+        "ln_scratch": torch.empty(native.layernorm_bwd_scratch_floats(R, C), **f32),
+        "ln_dg": torch.empty(C, **f32), "ln_db": torch.empty(C, **f32),
+        "attn_scratch": torch.empty(native.attention_bwd_scratch_floats(B, T, H), **f32),
+    }
+    model._ws = {key: ws}
+    return ws
+
+
+def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, grad_sink: Any = None,
+                          max_ctas: int = 0) -> torch.Tensor:
+    cfg = model.cfg
+    B, T = tokens.shape
+    C, H, V = cfg.n_embd, cfg.n_head, cfg.padded_vocab
+    R = B * T
+    dev = tokens.device
+    ws = _workspace(model, B, T, dev)
+    tokens = tokens.contiguous()
+    targets = targets.contiguous().view(-1)
+    eps = cfg.layer_norm_eps
+
+    def grad_of(p: nn.Parameter) -> torch.Tensor:
+        if grad_sink is not None:
+            return grad_sink.grad_view(p)
+        if p.grad is None:
+            p.grad = torch.empty_like(p)
+        return p.grad
+
+    def ready(*params: nn.Parameter) -> None:
+        if grad_sink is not None:
+            for p in params:
+                grad_sink.mark_ready(p)
+
+    def linear_fwd(x, lin: nn.Linear, out, *, act=0, d2=None, residual=None):
+        out_f, in_f = lin.weight.shape
+        native.gemm(x, lin.weight, out, m=R, n=out_f, k=in_f, bias=lin.bias, act=act, d2=d2, aux=residual,
+                    beta=1.0, max_ctas=max_ctas)
+
+    def linear_bwd(dy, x_in, lin: nn.Linear, dx_out, *, gelu_pre=None):
+        """dx = dy W (optionally * gelu'(pre)); then dW = dy^T x_in, db = colsum(dy) into the buckets."""
+        out_f, in_f = lin.weight.shape
+        if dx_out is not None:
+            native.gemm(dy, lin.weight, dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
+                        act=2 if gelu_pre is not None else 0, max_ctas=max_ctas)
+        native.gemm(dy, x_in, grad_of(lin.weight), m=out_f, n=in_f, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
+        native.colsum(dy, grad_of(lin.bias))
+        ready(lin.weight, lin.bias)
+
+    def ln_bwd(dy, x, ln: nn.LayerNorm, mean, rstd, dres, dx):
+        native.layernorm_bwd(dy, x, ln.weight, mean, rstd, dres, dx, ws["ln_dg"], ws["ln_db"], ws["ln_scratch"])
+        native.cast_f32_to_bf16(ws["ln_dg"], grad_of(ln.weight))
+        native.cast_f32_to_bf16(ws["ln_db"], grad_of(ln.bias))
+        ready(ln.weight, ln.bias)
+
+    # ------------------------------------------------------------------ forward
+    native.embedding_fwd(tokens, model.wte.weight, model.wpe.weight, ws["x0"])
+    x = ws["x0"]
+    for blk, a in zip(model.h, ws["blocks"]):
+        native.layernorm_fwd(x, None, blk.ln_1.weight, blk.ln_1.bias, a["a"], None, a["mean1"], a["rstd1"], eps)
+        linear_fwd(a["a"], blk.attn_qkv, a["qkv"])
+        native.attention_fwd(a["qkv"], a["att"], a["lse"], H)
+        linear_fwd(a["att"], blk.attn_proj, a["xm"], residual=x)
+        native.layernorm_fwd(a["xm"], None, blk.ln_2.weight, blk.ln_2.bias, a["m"], None, a["mean2"], a["rstd2"], eps)
+        linear_fwd(a["m"], blk.mlp_fc, a["h"], act=1, d2=a["z"])
+        linear_fwd(a["h"], blk.mlp_proj, a["x_out"], residual=a["xm"])
+        a["x_in"] = x
+        x = a["x_out"]
+    native.layernorm_fwd(x, None, model.ln_f.weight, model.ln_f.bias, ws["xf"], None, ws["meanf"], ws["rstdf"], eps)
+    native.gemm(ws["xf"], model.wte.weight, ws["logits"], m=R, n=V, k=C, max_ctas=max_ctas)
+    native.cross_entropy_fwd_bwd(ws["logits"], targets, ws["row_loss"], cfg.vocab_size, 1.0 / R)
+    native.mean_f32(ws["row_loss"], ws["loss"])
+
+    # ----------------------------------------------------------------- backward
+    dlogits = ws["logits"]
+    dxa, dxb = ws["dx"]
+    # LM head (tied): dxf = dlogits wte ; dwte = dlogits^T xf  (embedding gradient is added at the very end)
+    native.gemm(dlogits, model.wte.weight, ws["dC"], m=R, n=C, k=V, b_mn=True, max_ctas=max_ctas)
+    native.gemm(dlogits, ws["xf"], grad_of(model.wte.weight), m=V, n=C, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
+    ln_bwd(ws["dC"], x, model.ln_f, ws["meanf"], ws["rstdf"], None, dxa)
+    dx = dxa                                   # gradient w.r.t. the block output
+    other = dxb
+    for blk, a in zip(reversed(list(model.h)), reversed(ws["blocks"])):
+        # x_out = xm + h Wpr^T + b   -> dh (with GELU') ; dWpr, dbpr
+        linear_bwd(dx, a["h"], blk.mlp_proj, ws["d4C"], gelu_pre=a["z"])
+        # z = m Wfc^T + b            -> dm ; dWfc, dbfc
+        linear_bwd(ws["d4C"], a["m"], blk.mlp_fc, ws["dC"])
+        # m = LN2(xm); residual branch adds dx
+        ln_bwd(ws["dC"], a["xm"], blk.ln_2, a["mean2"], a["rstd2"], dx, other)
+        dxm = other
+        # xm = x_in + att Wo^T + b   -> datt ; dWo, dbo
+        linear_bwd(dxm, a["att"], blk.attn_proj, ws["dC"])
+        native.attention_bwd(a["qkv"], a["att"], ws["dC"], a["lse"], ws["dqkv"], ws["attn_scratch"], H)
+        # qkv = a Wqkv^T + b         -> da ; dWqkv, dbqkv
+        linear_bwd(ws["dqkv"].view(R, 3 * C), a["a"], blk.attn_qkv, ws["dC"])
+        # a = LN1(x_in); residual branch adds dxm
+        ln_bwd(ws["dC"], a["x_in"], blk.ln_1, a["mean1"], a["rstd1"], dxm, dx)
+        # dx now holds the gradient w.r.t. this block's input; `other` is free again
+    native.embedding_bwd(dx.view(B, T, C), tokens, grad_of(model.wte.weight), grad_of(model.wpe.weight))
+    ready(model.wpe.weight, model.wte.weight)
+    return ws["loss"]

@@ -256,7 +256,7 @@ class SymmComm(Communicator):
             if self.world_size > 1:
                 dist.barrier()
             return
-        native.comm_barrier(self.segments[0].desc, 15)
+        native.comm_barrier(self.segments[0].desc, 7)
         torch.cuda.current_stream().synchronize()
 
     def check_errors(self) -> None:

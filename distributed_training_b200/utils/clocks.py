@@ -38,6 +38,13 @@ class ClockSampler:
 
         self._thread = threading.Thread(target=pump, daemon=True)
         self._thread.start()
+        # nvidia-smi takes a while to produce its first line (longer with 8 ranks starting one each);
+        # wait for it so that the timed region is actually covered
+        import time
+
+        deadline = time.time() + 8.0
+        while not self.lines and time.time() < deadline:
+            time.sleep(0.02)
         return self
 
     def __exit__(self, *exc: Any) -> None:

@@ -159,8 +159,8 @@ int dtb_multi_tensor_adamw(const dtb_mt_args* args, float lr, float beta1, float
  * symmetric allocation.  `peers[r]` is rank r's heap base as mapped in THIS process;
  * `signals[r]` likewise for the signal pad (DTB_SIGNAL_PAD_BYTES, zero-initialised).
  * Operands are given as byte offsets into the heap, identical on all ranks.
- * `max_ctas` arguments: low 16 bits cap the grid (0 = default 32, at most 64 CTAs of 512 threads — the
- * SM budget left to concurrently running GEMMs); bits 16..19 select the barrier channel (0..15).
+ * `max_ctas` arguments: low 16 bits cap the grid (0 = default 64, at most 128 CTAs of 256 threads — the
+ * SM budget left to concurrently running GEMMs); bits 16..19 select the barrier channel (0..7).
  * Kernels that may run concurrently on different streams must use different channels; every rank
  * must issue the same sequence of collectives with the same arguments on a given channel. */
 #define DTB_MAX_RANKS 8

@@ -373,3 +373,27 @@ def test_single_gpu_fused_sgd_in_wgrad_epilogue_matches_reference():
     for (k, v), (_, rv) in zip(model.state_dict().items(), ref.state_dict().items()):
         assert torch.allclose(v.float(), rv, atol=3e-2, rtol=3e-2), (k, (v.float() - rv).abs().max())
     strategy.comm.close()
+
+
+def test_native_gpt2_step_matches_autograd():
+    from distributed_training_b200.models.gpt2 import GPT2, GPT2Config
+
+    torch.manual_seed(0)
+    cfg = GPT2Config(vocab_size=1000, n_positions=256, n_embd=128, n_layer=2, n_head=2)
+    model = GPT2(cfg, dtype=torch.bfloat16).to(DEV)
+    assert model.native_ready()
+    ref = GPT2(cfg, dtype=torch.float32).to(DEV)
+    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    tok = torch.randint(0, 1000, (2, 256), device=DEV)
+    tgt = torch.randint(0, 1000, (2, 256), device=DEV)
+    loss = model.forward_backward(tok, tgt)
+    ref_loss = ref.loss(tok, tgt)
+    ref_loss.backward()
+    assert abs(float(loss) - float(ref_loss.detach())) < 5e-2, (float(loss), float(ref_loss))
+    bad = []
+    for (name, p), (_, rp) in zip(model.named_parameters(), ref.named_parameters()):
+        scale = rp.grad.abs().max().item() + 1e-6
+        err = (p.grad.float() - rp.grad).abs().max().item()
+        if err > 0.08 * scale + 2e-4:
+            bad.append((name, err, scale))
+    assert not bad, bad[:6]
