@@ -49,15 +49,24 @@ constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);      // Q K^T, dO 
 constexpr uint32_t IDESC_PV = umma_idesc_bf16(128, 64, 0, 1);      // P V, dS K: A K-major, B MN-major
 constexpr uint32_t IDESC_TT = umma_idesc_bf16(128, 64, 1, 1);      // P^T dO, dS^T Q: both MN-major
 
-// K-major operand, one 64-wide K block: advance 32 B per UMMA_K
-__device__ __forceinline__ uint64_t desc_k(uint32_t base, int k16) { return umma_smem_desc(base + k16 * 32, 16, 1024); }
-// K-major operand spanning two 64-wide K blocks (P / dS as A with K = 128)
-__device__ __forceinline__ uint64_t desc_k2(uint32_t base, int k16) {
-  return umma_smem_desc(base + (k16 >> 2) * TILE_BYTES + (k16 & 3) * 32, 16, 1024);
+// Descriptor words are assembled from compile-time pieces so the issuing warp only adds immediates:
+//   hi = SBO (1024 B) | descriptor version 1 | 128-byte swizzle;  lo = start address >> 4 | LBO >> 4 << 16.
+constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint64_t mk_desc(uint32_t lo) { return (static_cast<uint64_t>(DESC_HI) << 32) | lo; }
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
 }
-// MN-major operand: K rows of 128 B, 8-row groups 1024 B apart, 64-wide MN blocks `lbo` apart
-__device__ __forceinline__ uint64_t desc_mn(uint32_t base, int k16, uint32_t lbo) {
-  return umma_smem_desc(base + k16 * 2048, lbo, 1024);
+// K-major operand, one 64-wide K block: advance 32 B per UMMA_K
+__device__ __forceinline__ uint64_t desc_k(uint32_t lo, int k16) { return mk_desc(lo + k16 * 2); }
+// K-major operand spanning two 64-wide K blocks (P / dS as A with K = 128)
+__device__ __forceinline__ uint64_t desc_k2(uint32_t lo, int k16) {
+  return mk_desc(lo + (k16 >> 2) * (TILE_BYTES >> 4) + (k16 & 3) * 2);
+}
+// MN-major operand: K rows of 128 B, 8-row groups 1024 B apart (K step = 2048 B), 64-wide MN blocks LBO apart
+__device__ __forceinline__ uint64_t desc_mn(uint32_t lo, int k16) { return mk_desc(lo + k16 * 128); }
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
 // -------------------------------------------------------------------------- forward
@@ -116,86 +125,95 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
 #pragma unroll
   for (int d = 0; d < HD; ++d) o[d] = 0.f;
 
+  const uint32_t q_lo = desc_lo(smem_u32(sQ), 16);
+  const uint32_t p_lo = desc_lo(smem_u32(sP), 16);
   for (int j = 0; j < n_kv; ++j) {
     const int st = j & 1;
-    if (tid == 0) {
-      if (j + 1 < n_kv) {
-        mbar_arrive_expect_tx(&kv_full[st ^ 1], 2 * TILE_BYTES);
-        tma_load_4d(sK + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], C + h * HD, row_base + (j + 1) * TK, 0, 0);
-        tma_load_4d(sV + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], 2 * C + h * HD, row_base + (j + 1) * TK, 0, 0);
-      }
+    if (warp == 0) {
+      // whole warp walks the control flow (uniform registers), one elected lane issues
       if (j == 0) mbar_wait(q_full, 0);
       mbar_wait(&kv_full[st], (j >> 1) & 1);
       tcgen05_fence_after();
-      const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * TILE_BYTES);
+      const uint32_t k_lo = desc_lo(smem_u32(sK + st * TILE_BYTES), 16);
+      if (elect_one()) {
+        if (j + 1 < n_kv) {
+          mbar_arrive_expect_tx(&kv_full[st ^ 1], 2 * TILE_BYTES);
+          tma_load_4d(sK + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], C + h * HD, row_base + (j + 1) * TK, 0, 0);
+          tma_load_4d(sV + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], 2 * C + h * HD, row_base + (j + 1) * TK, 0,
+                      0);
+        }
 #pragma unroll
-      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(qa, k), desc_k(ka, k), IDESC_S, k > 0);
-      umma_commit(s_done);
+        for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
+        umma_commit(s_done);
+      }
+      __syncwarp();
     }
     mbar_wait(s_done, j & 1);
     tcgen05_fence_after();
 
+    // the whole 128-column score row of this thread, read from TMEM once
+    uint32_t sv[128];
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t(&chunk)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sv[cc * 32]);
+      tmem_ld_32x32b_x32(tmem_row + cc * 32, chunk);
+    }
+    tmem_ld_wait();
     const bool diag = (j == qt);
     float tile_max = -INFINITY;
-#pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem_row + cc * 32, v);
-      tmem_ld_wait();
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const float s = __uint_as_float(v[e]);
-        if (!diag || cc * 32 + e <= tid) tile_max = fmaxf(tile_max, s);
-      }
+    for (int e = 0; e < 128; ++e) {
+      const float sc = __uint_as_float(sv[e]);
+      if (!diag || e <= tid) tile_max = fmaxf(tile_max, sc);
     }
     const float m_new = fmaxf(m, tile_max);
     const float alpha = exp2f((m - m_new) * c);
     const float mc = m_new * c;
     float rowsum = 0.f;
-#pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem_row + cc * 32, v);
-      tmem_ld_wait();
-      float p[32];
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const float s = __uint_as_float(v[e]);
-        p[e] = (!diag || cc * 32 + e <= tid) ? exp2f(fmaf(s, c, -mc)) : 0.f;
+    for (int q = 0; q < 16; ++q) {
+      float p[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int col = q * 8 + e;
+        p[e] = (!diag || col <= tid) ? exp2f(fmaf(__uint_as_float(sv[col]), c, -mc)) : 0.f;
         rowsum += p[e];
       }
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 pk;
-        pk.x = pack2(p[8 * q + 0], p[8 * q + 1]);
-        pk.y = pack2(p[8 * q + 2], p[8 * q + 3]);
-        pk.z = pack2(p[8 * q + 4], p[8 * q + 5]);
-        pk.w = pack2(p[8 * q + 6], p[8 * q + 7]);
-        *reinterpret_cast<uint4*>(sP + swz_chunk(tid, cc * 4 + q)) = pk;
-      }
+      uint4 pk;
+      pk.x = pack2(p[0], p[1]);
+      pk.y = pack2(p[2], p[3]);
+      pk.z = pack2(p[4], p[5]);
+      pk.w = pack2(p[6], p[7]);
+      *reinterpret_cast<uint4*>(sP + swz_chunk(tid, q)) = pk;
     }
     l = l * alpha + rowsum;
     m = m_new;
     fence_proxy_async_smem();
     tcgen05_fence_before();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0) {
       tcgen05_fence_after();
-      const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * TILE_BYTES);
+      const uint32_t v_lo = desc_lo(smem_u32(sV + st * TILE_BYTES), 8192);
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < TK / 16; ++k)
-        umma_f16<1>(tmem_base + 128, desc_k2(pa, k), desc_mn(va, k, 8192), IDESC_PV, k > 0);
-      umma_commit(o_done);
+        for (int k = 0; k < TK / 16; ++k)
+          umma_f16<1>(tmem_base + 128, desc_k2(p_lo, k), desc_mn(v_lo, k), IDESC_PV, k > 0);
+        umma_commit(o_done);
+      }
+      __syncwarp();
     }
     mbar_wait(o_done, j & 1);
     tcgen05_fence_after();
+    {
+      uint32_t ov[64];
 #pragma unroll
-    for (int cc = 0; cc < 2; ++cc) {
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem_row + 128 + cc * 32, v);
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t(&chunk)[32] = *reinterpret_cast<uint32_t(*)[32]>(&ov[cc * 32]);
+        tmem_ld_32x32b_x32(tmem_row + 128 + cc * 32, chunk);
+      }
       tmem_ld_wait();
 #pragma unroll
-      for (int e = 0; e < 32; ++e) o[cc * 32 + e] = o[cc * 32 + e] * alpha + __uint_as_float(v[e]);
+      for (int e = 0; e < 64; ++e) o[e] = o[e] * alpha + __uint_as_float(ov[e]);
     }
     tcgen05_fence_before();
   }
@@ -313,24 +331,31 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   const float c = scale * LOG2E;
   const long long stat_base = (static_cast<long long>(b) * H + h) * T;
 
+  const uint32_t k_lo = desc_lo(smem_u32(sK), 16), v_lo = desc_lo(smem_u32(sV), 16);
+  const uint32_t kmn_lo = desc_lo(smem_u32(sK), 8192);
+  const uint32_t p_mn_lo = desc_lo(smem_u32(sP), TILE_BYTES), ds_mn_lo = desc_lo(smem_u32(sdS), TILE_BYTES);
+  const uint32_t ds_k_lo = desc_lo(smem_u32(sdS), 16);
   for (int ii = 0; ii < n_q; ++ii) {
     const int it = jt + ii, st = ii & 1;
-    if (tid == 0) {
-      if (ii + 1 < n_q) {
-        mbar_arrive_expect_tx(&qdo_full[st ^ 1], 2 * TILE_BYTES);
-        tma_load_4d(sQ + (st ^ 1) * TILE_BYTES, &map_qkv, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
-        tma_load_4d(sdO + (st ^ 1) * TILE_BYTES, &map_do, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
-      }
+    if (warp == 0) {
       if (ii == 0) mbar_wait(kv_full, 0);
       mbar_wait(&qdo_full[st], (ii >> 1) & 1);
       tcgen05_fence_after();
-      const uint32_t qa = smem_u32(sQ + st * TILE_BYTES), doa = smem_u32(sdO + st * TILE_BYTES);
-      const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
+      const uint32_t q_lo = desc_lo(smem_u32(sQ + st * TILE_BYTES), 16);
+      const uint32_t do_lo = desc_lo(smem_u32(sdO + st * TILE_BYTES), 16);
+      if (elect_one()) {
+        if (ii + 1 < n_q) {
+          mbar_arrive_expect_tx(&qdo_full[st ^ 1], 2 * TILE_BYTES);
+          tma_load_4d(sQ + (st ^ 1) * TILE_BYTES, &map_qkv, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
+          tma_load_4d(sdO + (st ^ 1) * TILE_BYTES, &map_do, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
+        }
 #pragma unroll
-      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_S, desc_k(qa, k), desc_k(ka, k), IDESC_S, k > 0);
+        for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_S, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
 #pragma unroll
-      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_DP, desc_k(doa, k), desc_k(va, k), IDESC_S, k > 0);
-      umma_commit(sdp_done);
+        for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_DP, desc_k(do_lo, k), desc_k(v_lo, k), IDESC_S, k > 0);
+        umma_commit(sdp_done);
+      }
+      __syncwarp();
     }
     const float row_lse = lse[stat_base + it * TQ + tid] * LOG2E;
     const float row_delta = delta[stat_base + it * TQ + tid];
@@ -365,23 +390,26 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
     fence_proxy_async_smem();
     tcgen05_fence_before();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0) {
       tcgen05_fence_after();
-      const uint32_t pa = smem_u32(sP), dsa = smem_u32(sdS);
-      const uint32_t qa = smem_u32(sQ + st * TILE_BYTES), doa = smem_u32(sdO + st * TILE_BYTES), ka = smem_u32(sK);
-      // dV[kv,d] += sum_q P[q,kv] dO[q,d]      A = P^T (MN-major, kv blocks 16 KB apart), B = dO (MN-major)
+      const uint32_t qmn_lo = desc_lo(smem_u32(sQ + st * TILE_BYTES), 8192);
+      const uint32_t domn_lo = desc_lo(smem_u32(sdO + st * TILE_BYTES), 8192);
+      if (elect_one()) {
+        // dV[kv,d] += sum_q P[q,kv] dO[q,d]      A = P^T (MN-major, kv blocks 16 KB apart), B = dO (MN-major)
 #pragma unroll
-      for (int k = 0; k < TQ / 16; ++k)
-        umma_f16<1>(tmem_base + T_DV, desc_mn(pa, k, TILE_BYTES), desc_mn(doa, k, 8192), IDESC_TT, (ii | k) != 0);
-      // dK[kv,d] += sum_q dS[q,kv] Q[q,d]
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16<1>(tmem_base + T_DV, desc_mn(p_mn_lo, k), desc_mn(domn_lo, k), IDESC_TT, (ii | k) != 0);
+        // dK[kv,d] += sum_q dS[q,kv] Q[q,d]
 #pragma unroll
-      for (int k = 0; k < TQ / 16; ++k)
-        umma_f16<1>(tmem_base + T_DK, desc_mn(dsa, k, TILE_BYTES), desc_mn(qa, k, 8192), IDESC_TT, (ii | k) != 0);
-      // dQ[q,d] = sum_kv dS[q,kv] K[kv,d]       A = dS (K-major, two K blocks), B = K (MN-major)
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16<1>(tmem_base + T_DK, desc_mn(ds_mn_lo, k), desc_mn(qmn_lo, k), IDESC_TT, (ii | k) != 0);
+        // dQ[q,d] = sum_kv dS[q,kv] K[kv,d]       A = dS (K-major, two K blocks), B = K (MN-major)
 #pragma unroll
-      for (int k = 0; k < TK / 16; ++k)
-        umma_f16<1>(tmem_base + T_DQ, desc_k2(dsa, k), desc_mn(ka, k, 8192), IDESC_PV, k > 0);
-      umma_commit(grads_done);
+        for (int k = 0; k < TK / 16; ++k)
+          umma_f16<1>(tmem_base + T_DQ, desc_k2(ds_k_lo, k), desc_mn(kmn_lo, k), IDESC_PV, k > 0);
+        umma_commit(grads_done);
+      }
+      __syncwarp();
     }
     mbar_wait(grads_done, ii & 1);
     tcgen05_fence_after();
@@ -392,7 +420,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       tmem_ld_32x32b_x32(tmem_row + T_DQ + cc * 32, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int e = 0; e < 32; ++e) atomicAdd(dq_row + cc * 32 + e, __uint_as_float(v[e]));
+      for (int e = 0; e < 32; e += 4)
+        red_add_v4(dq_row + cc * 32 + e, __uint_as_float(v[e]), __uint_as_float(v[e + 1]), __uint_as_float(v[e + 2]),
+                   __uint_as_float(v[e + 3]));
     }
     tcgen05_fence_before();
   }

@@ -121,13 +121,18 @@ __global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16*
 // atomics are needed and the result is deterministic.
 constexpr int COLSUM_THREADS = 512;
 constexpr int COLSUM_ROWLANES = COLSUM_THREADS / 8;
+// gridDim.y row chunks: chunk y owns rows [y*rows_per_chunk, ...); with more than one chunk the
+// per-chunk sums go to `partial[y][cols]` (fp32) and colsum_finish_kernel adds them in chunk order.
 __global__ void __launch_bounds__(COLSUM_THREADS) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x,
                                                                      void* __restrict__ out, int rows, int cols,
-                                                                     long long ldx, int out_fp32) {
+                                                                     long long ldx, int out_fp32,
+                                                                     float* __restrict__ partial, int rows_per_chunk) {
   __shared__ float part[COLSUM_ROWLANES][65];
   const int cx = threadIdx.x & 7;    // column group within the CTA
   const int ry = threadIdx.x >> 3;   // row lane
   const int col = blockIdx.x * 64 + cx * 8;
+  x += static_cast<long long>(blockIdx.y) * rows_per_chunk * ldx;
+  rows = min(rows_per_chunk, rows - static_cast<int>(blockIdx.y) * rows_per_chunk);
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (col < cols) {
     if (col + 8 <= cols) {
@@ -169,10 +174,21 @@ __global__ void __launch_bounds__(COLSUM_THREADS) colsum_bf16_kernel(const __nv_
     for (int r = 0; r < COLSUM_ROWLANES; ++r) s += part[r][threadIdx.x];
     const int c = blockIdx.x * 64 + threadIdx.x;
     if (c < cols) {
-      if (out_fp32) reinterpret_cast<float*>(out)[c] = s;
+      if (partial != nullptr) partial[static_cast<long long>(blockIdx.y) * cols + c] = s;
+      else if (out_fp32) reinterpret_cast<float*>(out)[c] = s;
       else reinterpret_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16(s);
     }
   }
+}
+
+__global__ void __launch_bounds__(256) colsum_finish_kernel(const float* __restrict__ partial, int chunks, int cols,
+                                                            void* __restrict__ out, int out_fp32) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (int y = 0; y < chunks; ++y) s += partial[static_cast<long long>(y) * cols + c];
+  if (out_fp32) reinterpret_cast<float*>(out)[c] = s;
+  else reinterpret_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16(s);
 }
 
 __device__ __forceinline__ float block_sum(float v, float* smem) {
@@ -269,7 +285,36 @@ extern "C" int dtb_colsum_bf16(const void* x, void* out, int rows, int cols, lon
   DTB_REQUIRE(rows > 0 && cols > 0, "dtb_colsum_bf16: empty input");
   DTB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "dtb_colsum_bf16: x must be 16-byte aligned");
   colsum_bf16_kernel<<<(cols + 63) / 64, COLSUM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), out, rows, cols, ldx, out_fp32);
+      static_cast<const __nv_bfloat16*>(x), out, rows, cols, ldx, out_fp32, nullptr, rows);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" size_t dtb_colsum_split_scratch_floats(int rows, int cols) {
+  (void)rows;
+  return static_cast<size_t>(DTB_COLSUM_MAX_CHUNKS) * static_cast<size_t>(cols);
+}
+
+extern "C" int dtb_colsum_bf16_split(const void* x, void* out, int rows, int cols, long long ldx, int out_fp32,
+                                     float* scratch, void* stream) {
+  DTB_REQUIRE(rows > 0 && cols > 0, "dtb_colsum_bf16_split: empty input");
+  DTB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+              "dtb_colsum_bf16_split: x must be 16-byte aligned");
+  DTB_REQUIRE(scratch != nullptr, "dtb_colsum_bf16_split: scratch is required");
+  // enough row chunks to put ~2 CTAs on every SM, at least 256 rows each
+  const int col_blocks = (cols + 63) / 64;
+  int chunks = (2 * sm_count() + col_blocks - 1) / col_blocks;
+  if (chunks > DTB_COLSUM_MAX_CHUNKS) chunks = DTB_COLSUM_MAX_CHUNKS;
+  if (chunks > (rows + 255) / 256) chunks = (rows + 255) / 256;
+  if (chunks < 1) chunks = 1;
+  const int rows_per_chunk = (rows + chunks - 1) / chunks;
+  chunks = (rows + rows_per_chunk - 1) / rows_per_chunk;
+  auto s = static_cast<cudaStream_t>(stream);
+  if (chunks == 1) return dtb_colsum_bf16(x, out, rows, cols, ldx, out_fp32, stream);
+  colsum_bf16_kernel<<<dim3(col_blocks, chunks), COLSUM_THREADS, 0, s>>>(static_cast<const __nv_bfloat16*>(x), out, rows,
+                                                                         cols, ldx, out_fp32, scratch, rows_per_chunk);
+  DTB_LAUNCH_OK();
+  colsum_finish_kernel<<<(cols + 255) / 256, 256, 0, s>>>(scratch, chunks, cols, out, out_fp32);
   DTB_LAUNCH_OK();
   return 0;
 }

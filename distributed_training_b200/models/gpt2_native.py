@@ -103,7 +103,7 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
             native.gemm(dy, lin.weight, dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
                         act=2 if gelu_pre is not None else 0, max_ctas=max_ctas)
         native.gemm(dy, x_in, grad_of(lin.weight), m=out_f, n=in_f, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
-        native.colsum(dy, grad_of(lin.bias))
+        native.colsum_split(dy, grad_of(lin.bias))
         ready(lin.weight, lin.bias)
 
     def ln_bwd(dy, x, ln: nn.LayerNorm, mean, rstd, dres, dx):

@@ -139,7 +139,7 @@ class MLP(nn.Module):
                 native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
                             lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
             if layer.bias is not None:
-                native.colsum(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
+                native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
             if grad_sink is not None:
                 grad_sink.mark_ready(layer.weight)
                 if layer.bias is not None:

@@ -198,6 +198,23 @@ def colsum(x2d: torch.Tensor, out: torch.Tensor, ldx: Optional[int] = None):
     return out
 
 
+_COLSUM_SCRATCH = {}
+
+
+def colsum_split(x2d: torch.Tensor, out: torch.Tensor, ldx: Optional[int] = None):
+    """Column sums with the rows split across CTAs (tall, narrow inputs); scratch is cached per device."""
+    rows, cols = x2d.shape
+    need = 64 * cols
+    key = x2d.device
+    buf = _COLSUM_SCRATCH.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(max(need, 64 * 8192), dtype=torch.float32, device=x2d.device)
+        _COLSUM_SCRATCH[key] = buf
+    _ok(lib().dtb_colsum_bf16_split(_p(x2d), _p(out), rows, cols, C.c_longlong(ldx if ldx is not None else cols),
+                                    int(out.dtype == torch.float32), _p(buf), _stream()))
+    return out
+
+
 def cast_f32_to_bf16(src, dst):
     _ok(lib().dtb_cast_f32_to_bf16(_p(src), _p(dst), C.c_longlong(src.numel()), _stream()))
     return dst

@@ -73,6 +73,13 @@ int dtb_gelu_fwd_bf16(const void* x, void* y, long long n, void* stream);
 int dtb_gelu_bwd_bf16(const void* x, const void* dy, void* dx, long long n, void* stream);
 /* out[n] = sum_m x[m,n]  (bias gradient). bf16 in, out bf16 or fp32. Uses no scratch. */
 int dtb_colsum_bf16(const void* x, void* out, int rows, int cols, long long ldx, int out_fp32, void* stream);
+/* Same result with the rows split over up to DTB_COLSUM_MAX_CHUNKS CTAs per column block (narrow, tall
+ * inputs such as [8192, 768] would otherwise occupy 12 CTAs); partial sums go through `scratch`
+ * (dtb_colsum_split_scratch_floats floats) and are added in a fixed order (deterministic). */
+#define DTB_COLSUM_MAX_CHUNKS 64
+size_t dtb_colsum_split_scratch_floats(int rows, int cols);
+int dtb_colsum_bf16_split(const void* x, void* out, int rows, int cols, long long ldx, int out_fp32, float* scratch,
+                          void* stream);
 int dtb_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
 int dtb_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 int dtb_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
