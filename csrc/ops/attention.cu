@@ -70,7 +70,8 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 }
 
 // -------------------------------------------------------------------------- forward
-constexpr int FWD_SMEM = TILE_BYTES * (1 + 2 + 2 + 2) + 1024 + 128;
+// Q, K x2 stages, V (single buffer), P: 96 KB + slack, so two CTAs fit on one SM
+constexpr int FWD_SMEM = TILE_BYTES * (1 + 2 + 1 + 2) + 1024 + 128;
 
 __global__ void __launch_bounds__(128, 2)
 fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, float* __restrict__ lse,
@@ -79,14 +80,15 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + TILE_BYTES;            // 2 stages
-  uint8_t* sV = sK + 2 * TILE_BYTES;        // 2 stages
-  uint8_t* sP = sV + 2 * TILE_BYTES;        // [128 x 128] bf16
+  uint8_t* sV = sK + 2 * TILE_BYTES;        // single buffer: reloaded once P V of the previous tile is done
+  uint8_t* sP = sV + TILE_BYTES;            // [128 x 128] bf16
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * TILE_BYTES);
   uint64_t* q_full = bars;
-  uint64_t* kv_full = bars + 1;             // [2]
-  uint64_t* s_done = bars + 3;
-  uint64_t* o_done = bars + 4;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 5);
+  uint64_t* k_full = bars + 1;              // [2]
+  uint64_t* v_full = bars + 3;
+  uint64_t* s_done = bars + 4;
+  uint64_t* o_done = bars + 5;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 6);
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int qt = gridDim.x - 1 - blockIdx.x;          // longest rows first
@@ -98,8 +100,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
   if (tid == 0) {
     prefetch_tensormap(&map_qkv);
     mbar_init(q_full, 1);
-    mbar_init(&kv_full[0], 1);
-    mbar_init(&kv_full[1], 1);
+    mbar_init(&k_full[0], 1);
+    mbar_init(&k_full[1], 1);
+    mbar_init(v_full, 1);
     mbar_init(s_done, 1);
     mbar_init(o_done, 1);
     fence_barrier_init();
@@ -114,9 +117,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
   if (tid == 0) {
     mbar_arrive_expect_tx(q_full, TILE_BYTES);
     tma_load_4d(sQ, &map_qkv, q_full, h * HD, row_base + qt * TQ, 0, 0);
-    mbar_arrive_expect_tx(&kv_full[0], 2 * TILE_BYTES);
-    tma_load_4d(sK, &map_qkv, &kv_full[0], C + h * HD, row_base, 0, 0);
-    tma_load_4d(sV, &map_qkv, &kv_full[0], 2 * C + h * HD, row_base, 0, 0);
+    mbar_arrive_expect_tx(&k_full[0], TILE_BYTES);
+    tma_load_4d(sK, &map_qkv, &k_full[0], C + h * HD, row_base, 0, 0);
+    mbar_arrive_expect_tx(v_full, TILE_BYTES);
+    tma_load_4d(sV, &map_qkv, v_full, 2 * C + h * HD, row_base, 0, 0);
   }
 
   const float c = scale * LOG2E;
@@ -127,27 +131,28 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
 
   const uint32_t q_lo = desc_lo(smem_u32(sQ), 16);
   const uint32_t p_lo = desc_lo(smem_u32(sP), 16);
+  const uint32_t v_lo = desc_lo(smem_u32(sV), 8192);
+  // Software pipeline: the S = Q K^T MMAs of tile j+1 are issued right behind the P V MMAs of tile j, so the
+  // tensor core works on the next scores while the threads fold P V into O.  Prologue: S of tile 0.
+  if (warp == 0) {
+    mbar_wait(q_full, 0);
+    mbar_wait(&k_full[0], 0);
+    tcgen05_fence_after();
+    const uint32_t k_lo = desc_lo(smem_u32(sK), 16);
+    if (elect_one()) {
+      if (n_kv > 1) {
+        mbar_arrive_expect_tx(&k_full[1], TILE_BYTES);
+        tma_load_4d(sK + TILE_BYTES, &map_qkv, &k_full[1], C + h * HD, row_base + TK, 0, 0);
+      }
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
+      umma_commit(s_done);
+    }
+    __syncwarp();
+  }
   for (int j = 0; j < n_kv; ++j) {
     const int st = j & 1;
-    if (warp == 0) {
-      // whole warp walks the control flow (uniform registers), one elected lane issues
-      if (j == 0) mbar_wait(q_full, 0);
-      mbar_wait(&kv_full[st], (j >> 1) & 1);
-      tcgen05_fence_after();
-      const uint32_t k_lo = desc_lo(smem_u32(sK + st * TILE_BYTES), 16);
-      if (elect_one()) {
-        if (j + 1 < n_kv) {
-          mbar_arrive_expect_tx(&kv_full[st ^ 1], 2 * TILE_BYTES);
-          tma_load_4d(sK + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], C + h * HD, row_base + (j + 1) * TK, 0, 0);
-          tma_load_4d(sV + (st ^ 1) * TILE_BYTES, &map_qkv, &kv_full[st ^ 1], 2 * C + h * HD, row_base + (j + 1) * TK, 0,
-                      0);
-        }
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
-        umma_commit(s_done);
-      }
-      __syncwarp();
-    }
+    const bool more = (j + 1 < n_kv);
     mbar_wait(s_done, j & 1);
     tcgen05_fence_after();
 
@@ -192,18 +197,39 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
     tcgen05_fence_before();
     __syncthreads();
     if (warp == 0) {
+      mbar_wait(v_full, j & 1);
+      if (more) mbar_wait(&k_full[st ^ 1], ((j + 1) >> 1) & 1);
       tcgen05_fence_after();
-      const uint32_t v_lo = desc_lo(smem_u32(sV + st * TILE_BYTES), 8192);
+      const uint32_t kn_lo = desc_lo(smem_u32(sK + (st ^ 1) * TILE_BYTES), 16);
       if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < TK / 16; ++k)
           umma_f16<1>(tmem_base + 128, desc_k2(p_lo, k), desc_mn(v_lo, k), IDESC_PV, k > 0);
         umma_commit(o_done);
+        if (more) {   // every thread has read S of tile j (the __syncthreads above): its TMEM columns are free
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(q_lo, k), desc_k(kn_lo, k), IDESC_S, k > 0);
+          umma_commit(s_done);
+        }
       }
       __syncwarp();
     }
     mbar_wait(o_done, j & 1);
     tcgen05_fence_after();
+    if (warp == 0) {
+      // P V of tile j is complete: V's buffer and K stage `st` (read by S of tile j) can be refilled
+      if (elect_one()) {
+        if (more) {
+          mbar_arrive_expect_tx(v_full, TILE_BYTES);
+          tma_load_4d(sV, &map_qkv, v_full, 2 * C + h * HD, row_base + (j + 1) * TK, 0, 0);
+        }
+        if (j + 2 < n_kv) {
+          mbar_arrive_expect_tx(&k_full[st], TILE_BYTES);
+          tma_load_4d(sK + st * TILE_BYTES, &map_qkv, &k_full[st], C + h * HD, row_base + (j + 2) * TK, 0, 0);
+        }
+      }
+      __syncwarp();
+    }
     {
       uint32_t ov[64];
 #pragma unroll
@@ -335,28 +361,29 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   const uint32_t kmn_lo = desc_lo(smem_u32(sK), 8192);
   const uint32_t p_mn_lo = desc_lo(smem_u32(sP), TILE_BYTES), ds_mn_lo = desc_lo(smem_u32(sdS), TILE_BYTES);
   const uint32_t ds_k_lo = desc_lo(smem_u32(sdS), 16);
+  // Software pipeline: S and dP of query tile i+1 are issued right behind the dV/dK/dQ MMAs of tile i.
+  if (warp == 0) {
+    mbar_wait(kv_full, 0);
+    mbar_wait(&qdo_full[0], 0);
+    tcgen05_fence_after();
+    const uint32_t q_lo = desc_lo(smem_u32(sQ), 16), do_lo = desc_lo(smem_u32(sdO), 16);
+    if (elect_one()) {
+      if (n_q > 1) {
+        mbar_arrive_expect_tx(&qdo_full[1], 2 * TILE_BYTES);
+        tma_load_4d(sQ + TILE_BYTES, &map_qkv, &qdo_full[1], h * HD, row_base + (jt + 1) * TQ, 0, 0);
+        tma_load_4d(sdO + TILE_BYTES, &map_do, &qdo_full[1], h * HD, row_base + (jt + 1) * TQ, 0, 0);
+      }
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_S, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_DP, desc_k(do_lo, k), desc_k(v_lo, k), IDESC_S, k > 0);
+      umma_commit(sdp_done);
+    }
+    __syncwarp();
+  }
   for (int ii = 0; ii < n_q; ++ii) {
     const int it = jt + ii, st = ii & 1;
-    if (warp == 0) {
-      if (ii == 0) mbar_wait(kv_full, 0);
-      mbar_wait(&qdo_full[st], (ii >> 1) & 1);
-      tcgen05_fence_after();
-      const uint32_t q_lo = desc_lo(smem_u32(sQ + st * TILE_BYTES), 16);
-      const uint32_t do_lo = desc_lo(smem_u32(sdO + st * TILE_BYTES), 16);
-      if (elect_one()) {
-        if (ii + 1 < n_q) {
-          mbar_arrive_expect_tx(&qdo_full[st ^ 1], 2 * TILE_BYTES);
-          tma_load_4d(sQ + (st ^ 1) * TILE_BYTES, &map_qkv, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
-          tma_load_4d(sdO + (st ^ 1) * TILE_BYTES, &map_do, &qdo_full[st ^ 1], h * HD, row_base + (it + 1) * TQ, 0, 0);
-        }
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_S, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_DP, desc_k(do_lo, k), desc_k(v_lo, k), IDESC_S, k > 0);
-        umma_commit(sdp_done);
-      }
-      __syncwarp();
-    }
+    const bool more = (ii + 1 < n_q);
     const float row_lse = lse[stat_base + it * TQ + tid] * LOG2E;
     const float row_delta = delta[stat_base + it * TQ + tid];
     mbar_wait(sdp_done, ii & 1);
@@ -391,9 +418,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
     tcgen05_fence_before();
     __syncthreads();
     if (warp == 0) {
+      if (more) mbar_wait(&qdo_full[st ^ 1], ((ii + 1) >> 1) & 1);
       tcgen05_fence_after();
       const uint32_t qmn_lo = desc_lo(smem_u32(sQ + st * TILE_BYTES), 8192);
       const uint32_t domn_lo = desc_lo(smem_u32(sdO + st * TILE_BYTES), 8192);
+      const uint32_t qn_lo = desc_lo(smem_u32(sQ + (st ^ 1) * TILE_BYTES), 16);
+      const uint32_t don_lo = desc_lo(smem_u32(sdO + (st ^ 1) * TILE_BYTES), 16);
       if (elect_one()) {
         // dV[kv,d] += sum_q P[q,kv] dO[q,d]      A = P^T (MN-major, kv blocks 16 KB apart), B = dO (MN-major)
 #pragma unroll
@@ -408,11 +438,29 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
         for (int k = 0; k < TK / 16; ++k)
           umma_f16<1>(tmem_base + T_DQ, desc_k2(ds_k_lo, k), desc_mn(kmn_lo, k), IDESC_PV, k > 0);
         umma_commit(grads_done);
+        if (more) {   // S / dP columns were fully read before the __syncthreads above
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k)
+            umma_f16<1>(tmem_base + T_S, desc_k(qn_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k)
+            umma_f16<1>(tmem_base + T_DP, desc_k(don_lo, k), desc_k(v_lo, k), IDESC_S, k > 0);
+          umma_commit(sdp_done);
+        }
       }
       __syncwarp();
     }
     mbar_wait(grads_done, ii & 1);
     tcgen05_fence_after();
+    if (warp == 0 && ii + 2 < n_q) {
+      // the MMAs that read Q / dO of tile i are done: refill this stage with tile i+2
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&qdo_full[st], 2 * TILE_BYTES);
+        tma_load_4d(sQ + st * TILE_BYTES, &map_qkv, &qdo_full[st], h * HD, row_base + (it + 2) * TQ, 0, 0);
+        tma_load_4d(sdO + st * TILE_BYTES, &map_do, &qdo_full[st], h * HD, row_base + (it + 2) * TQ, 0, 0);
+      }
+      __syncwarp();
+    }
     float* dq_row = dq_acc + (stat_base + it * TQ + tid) * HD;
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
