@@ -44,7 +44,19 @@ struct Params {
   int act;
   float alpha, beta;
   uint32_t lbo_a, sbo_a, lbo_b, sbo_b;   // UMMA descriptor byte offsets
+  // ---- all-gather fusion (GATHER kernels): B = weights [N, K], rows sharded evenly over g_world ranks.
+  // Gather warps pull 16-row pieces of every rank's shard (peer-mapped) into the local full matrix that
+  // map_b describes and bump the piece's n-block counter; the TMA producer acquires the counter before it
+  // loads a tile of that n-block.  Tiles are visited own-rows-first so transfers run ahead of the MMAs.
+  const void* g_peer_shard[DTB_MAX_RANKS];
+  void* g_full;
+  int* g_flags;            // [n_blocks] arrival counters, then one work counter; zeroed before launch
+  long long g_ldb;
+  int g_world, g_rank, g_rows_per_rank;
+  int g_rotate;            // n-blocks to rotate the visiting order by (rank * blocks_per_rank); -1 = off
 };
+
+constexpr int GATHER_ROWS = 16;      // rows per gather piece
 
 template <int CG, int BN>
 struct Config {
@@ -86,6 +98,11 @@ __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& bi, 
   const int per_batch = p.m_blocks * p.n_blocks;
   bi = tile / per_batch;
   int t = tile - bi * per_batch;
+  if (p.g_rotate >= 0) {   // all m-blocks of one n-block, n-blocks starting at this rank's own rows
+    m_blk = t % p.m_blocks;
+    n_blk = (t / p.m_blocks + p.g_rotate) % p.n_blocks;
+    return;
+  }
   const int group_size = p.group_m * p.n_blocks;
   const int group_id = t / group_size;
   const int first_m = group_id * p.group_m;
@@ -207,8 +224,10 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&raw)[
   }
 }
 
-template <int CG, int BN, int A_MN, int B_MN>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+constexpr int NUM_GATHER_WARPS = 2;
+
+template <int CG, int BN, int A_MN, int B_MN, bool GATHER = false>
+__global__ void __launch_bounds__(NUM_THREADS + (GATHER ? 32 * NUM_GATHER_WARPS : 0), 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Params p) {
   using Cfg = Config<CG, BN>;
   constexpr int STAGES = Cfg::STAGES;
@@ -271,6 +290,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
       const int m0 = (m_blk * CG + static_cast<int>(cta_rank)) * BM;
       const int n0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;
+      if constexpr (GATHER) {
+        // every 16-row piece of this n-block has landed in the local matrix (written with generic stores by
+        // gather warps of any CTA): acquire the counter, then order the async-proxy (TMA) reads after it
+        const int want = (min(BN, p.N - n_blk * BN) + GATHER_ROWS - 1) / GATHER_ROWS;
+        while (ld_acquire_gpu(reinterpret_cast<const uint32_t*>(p.g_flags + n_blk)) < static_cast<uint32_t>(want)) {
+        }
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+      }
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
@@ -374,7 +401,47 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         if (acc == 0) acc_phase ^= 1;
       }
     }
-  } else {
+  } else if (GATHER && warp >= NUM_THREADS / 32) {
+    // ============================ gather warps ============================
+    // Pieces are claimed from a global counter in the order the tiles will need them.
+    const int pieces_per_block = BN / GATHER_ROWS;
+    const int total_pieces = p.n_blocks * pieces_per_block;
+    int* work = p.g_flags + p.n_blocks;
+    const long long row_bytes = static_cast<long long>(p.K) * 2;
+    while (true) {
+      int piece = 0;
+      if (lane == 0) piece = atomicAdd(work, 1);
+      piece = __shfl_sync(0xffffffffu, piece, 0);
+      if (piece >= total_pieces) break;
+      const int n_blk = (piece / pieces_per_block + p.g_rotate) % p.n_blocks;
+      const int r0 = n_blk * BN + (piece % pieces_per_block) * GATHER_ROWS;
+      if (r0 < p.N) {
+        const int owner = r0 / p.g_rows_per_rank;
+        const int nrows = min(GATHER_ROWS, p.N - r0);
+        const uint8_t* src = static_cast<const uint8_t*>(p.g_peer_shard[owner]) +
+                             static_cast<long long>(r0 - owner * p.g_rows_per_rank) * p.g_ldb * 2;
+        uint8_t* dst = static_cast<uint8_t*>(p.g_full) + static_cast<long long>(r0) * p.g_ldb * 2;
+        for (int r = 0; r < nrows; ++r) {
+          const uint8_t* srow = src + static_cast<long long>(r) * p.g_ldb * 2;
+          uint8_t* drow = dst + static_cast<long long>(r) * p.g_ldb * 2;
+          long long off = static_cast<long long>(lane) * 16;
+          for (; off + 7 * 512 < row_bytes; off += 8 * 512) {   // 8 x 16 B per lane in flight
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = ld_nc_v4(srow + off + u * 512);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) st_v4(drow + off + u * 512, v[u]);
+          }
+          for (; off < row_bytes; off += 512) st_v4(drow + off, ld_nc_v4(srow + off));
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence();
+        atomicAdd(p.g_flags + n_blk, 1);
+      }
+    }
+  } else if (warp < NUM_THREADS / 32) {
     // ============================== epilogue ==============================
     const int quad = warp & 3;   // TMEM lane quadrant this warp may access
     int acc = 0;
@@ -455,10 +522,10 @@ static int make_operand_map(CUtensorMap* map, const void* base, int mn_major, in
   return get_tensor_map_bf16(map, base, dims, strides, box);
 }
 
-template <int CG, int BN, int A_MN, int B_MN>
+template <int CG, int BN, int A_MN, int B_MN, bool GATHER = false>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int grid, cudaStream_t stream) {
   using Cfg = Config<CG, BN>;
-  auto kernel = gemm_kernel<CG, BN, A_MN, B_MN>;
+  auto kernel = gemm_kernel<CG, BN, A_MN, B_MN, GATHER>;
   static bool configured = false;
   if (!configured) {
     DTB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -466,7 +533,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p,
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
-  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.blockDim = dim3(NUM_THREADS + (GATHER ? 32 * NUM_GATHER_WARPS : 0));
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -493,7 +560,7 @@ static int dispatch_major(const CUtensorMap& ma, const CUtensorMap& mb, const Pa
 }  // namespace gemm
 }  // namespace dtb
 
-extern "C" int dtb_gemm_bf16(const dtb_gemm_args* a, void* stream) {
+static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* stream) {
   using namespace dtb;
   using namespace dtb::gemm;
   DTB_REQUIRE(a != nullptr, "dtb_gemm_bf16: null args");
@@ -546,6 +613,30 @@ extern "C" int dtb_gemm_bf16(const dtb_gemm_args* a, void* stream) {
   p.sbo_a = a->dbg_sbo_a ? a->dbg_sbo_a : 1024u;
   p.lbo_b = a->dbg_lbo_b ? a->dbg_lbo_b : (a->b_mn_major ? 8192u : 16u);
   p.sbo_b = a->dbg_sbo_b ? a->dbg_sbo_b : 1024u;
+  p.g_rotate = -1;
+  if (g != nullptr) {
+    DTB_REQUIRE(!a->a_mn_major && !a->b_mn_major && bi * bo == 1,
+                "dtb_gemm_bf16_allgather: forward layout only (A, B K-major, no batch)");
+    DTB_REQUIRE(g->world >= 1 && g->world <= DTB_MAX_RANKS && g->rank >= 0 && g->rank < g->world,
+                "dtb_gemm_bf16_allgather: bad rank/world");
+    DTB_REQUIRE(g->rows_per_rank > 0 && g->rows_per_rank % GATHER_ROWS == 0 &&
+                    static_cast<long long>(g->rows_per_rank) * g->world >= a->n,
+                "dtb_gemm_bf16_allgather: rows_per_rank must be a multiple of %d and cover N", GATHER_ROWS);
+    DTB_REQUIRE(g->flags != nullptr, "dtb_gemm_bf16_allgather: flags scratch is required");
+    DTB_REQUIRE(a->k % 8 == 0, "dtb_gemm_bf16_allgather: K must be a multiple of 8");
+    for (int r = 0; r < g->world; ++r) {
+      DTB_REQUIRE(g->peer_shard[r] != nullptr && (reinterpret_cast<uintptr_t>(g->peer_shard[r]) & 15) == 0,
+                  "dtb_gemm_bf16_allgather: shard pointer of rank %d missing or unaligned", r);
+      p.g_peer_shard[r] = g->peer_shard[r];
+    }
+    p.g_full = const_cast<void*>(a->b);
+    p.g_flags = g->flags;
+    p.g_ldb = a->ldb;
+    p.g_world = g->world; p.g_rank = g->rank; p.g_rows_per_rank = g->rows_per_rank;
+    // own rows first: start the n-block walk at the block holding this rank's first row
+    p.g_rotate = static_cast<int>((static_cast<long long>(g->rank) * g->rows_per_rank / bn) % p.n_blocks);
+    DTB_CUDA_OK(cudaMemsetAsync(g->flags, 0, sizeof(int) * (p.n_blocks + 1), static_cast<cudaStream_t>(stream)));
+  }
 
   CUtensorMap ma, mb;
   if (make_operand_map(&ma, a->a, a->a_mn_major, a->m, a->k, a->lda, bi, bo, a->a_stride_inner, a->a_stride_outer, BM))
@@ -566,7 +657,21 @@ extern "C" int dtb_gemm_bf16(const dtb_gemm_args* a, void* stream) {
     grid = static_cast<int>(tiles < max_ctas ? tiles : max_ctas);
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (g != nullptr) {
+    if (cg == 2) return launch<2, 256, 0, 0, true>(ma, mb, p, grid, s);
+    if (bn == 256) return launch<1, 256, 0, 0, true>(ma, mb, p, grid, s);
+    return launch<1, 128, 0, 0, true>(ma, mb, p, grid, s);
+  }
   if (cg == 2) return dispatch_major<2, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
   if (bn == 256) return dispatch_major<1, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
   return dispatch_major<1, 128>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
 }
+
+extern "C" int dtb_gemm_bf16(const dtb_gemm_args* a, void* stream) { return gemm_impl(a, nullptr, stream); }
+
+extern "C" int dtb_gemm_bf16_allgather(const dtb_gemm_args* a, const dtb_gather_args* g, void* stream) {
+  DTB_REQUIRE(g != nullptr, "dtb_gemm_bf16_allgather: null gather args");
+  return gemm_impl(a, g, stream);
+}
+
+extern "C" size_t dtb_gemm_allgather_flag_ints(int n) { return static_cast<size_t>((n + 127) / 128 + 1); }

@@ -69,7 +69,7 @@ class Block(nn.Module):
 
 
 class GPT2(nn.Module):
-    supports_sharded_native = False
+    supports_sharded_native = True
 
     def __init__(self, cfg: GPT2Config, dtype: torch.dtype = torch.float32) -> None:
         super().__init__()

@@ -91,10 +91,17 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
             for p in params:
                 grad_sink.mark_ready(p)
 
+    # a sharded grad_sink gathers each weight inside the first GEMM that consumes it
+    gemm_fwd = getattr(grad_sink, "gemm_forward", None) or native.gemm
+    ensure = getattr(grad_sink, "ensure_gathered", None)
+    if ensure is not None:      # the embedding lookup reads the tables before any GEMM does
+        ensure(model.wte.weight)
+        ensure(model.wpe.weight)
+
     def linear_fwd(x, lin: nn.Linear, out, *, act=0, d2=None, residual=None):
         out_f, in_f = lin.weight.shape
-        native.gemm(x, lin.weight, out, m=R, n=out_f, k=in_f, bias=lin.bias, act=act, d2=d2, aux=residual,
-                    beta=1.0, max_ctas=max_ctas)
+        gemm_fwd(x, lin.weight, out, m=R, n=out_f, k=in_f, bias=lin.bias, act=act, d2=d2, aux=residual,
+                 beta=1.0, max_ctas=max_ctas)
 
     def linear_bwd(dy, x_in, lin: nn.Linear, dx_out, *, gelu_pre=None):
         """dx = dy W (optionally * gelu'(pre)); then dW = dy^T x_in, db = colsum(dy) into the buckets."""

@@ -25,7 +25,7 @@ from ..ops import native
 class MLP(nn.Module):
     """``num_layers`` Linear layers with tanh-GELU between them."""
 
-    supports_sharded_native = False
+    supports_sharded_native = True
 
     def __init__(self, input_size: int, hidden_size: int, output_size: int, num_layers: int = 2,
                  dtype: torch.dtype = torch.float32, bias: bool = True) -> None:
@@ -99,17 +99,19 @@ class MLP(nn.Module):
                 p.grad = torch.empty_like(p)
             return p.grad
 
+        # a sharded grad_sink gathers the weight inside the forward GEMM (all-gather -> GEMM fusion)
+        gemm_fwd = getattr(grad_sink, "gemm_forward", None) or native.gemm
         # ---- forward: h_{i+1} = gelu(h_i W_i^T + b_i), pre-activation kept for backward
         h = x
         for i, layer in enumerate(self.layers):
             out_f, in_f = layer.weight.shape
             if i != n - 1:
-                native.gemm(h, layer.weight, ws["h"][i], m=rows, n=out_f, k=in_f, bias=layer.bias, act=1,
-                            d2=ws["z"][i], max_ctas=max_ctas)
+                gemm_fwd(h, layer.weight, ws["h"][i], m=rows, n=out_f, k=in_f, bias=layer.bias, act=1,
+                         d2=ws["z"][i], max_ctas=max_ctas)
                 h = ws["h"][i]
             else:
-                native.gemm(h, layer.weight, ws["logits"], m=rows, n=out_f, k=in_f, bias=layer.bias,
-                            max_ctas=max_ctas)
+                gemm_fwd(h, layer.weight, ws["logits"], m=rows, n=out_f, k=in_f, bias=layer.bias,
+                         max_ctas=max_ctas)
         # ---- loss + dlogits in place
         native.cross_entropy_fwd_bwd(ws["logits"], targets, ws["row_loss"], self.dims[-1], 1.0 / rows)
         native.mean_f32(ws["row_loss"], ws["loss"])

@@ -162,6 +162,47 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, m: int, n: int,
     return out
 
 
+class GatherArgs(C.Structure):
+    _fields_ = [("peer_shard", C.c_void_p * MAX_RANKS), ("flags", C.c_void_p),
+                ("world", C.c_int), ("rank", C.c_int), ("rows_per_rank", C.c_int)]
+
+
+def gemm_allgather_flag_ints(n: int) -> int:
+    return (n + 127) // 128 + 1
+
+
+def gemm_allgather(a: torch.Tensor, b_full: torch.Tensor, out: torch.Tensor, peer_shard_ptrs: Sequence[int],
+                   flags: torch.Tensor, rank: int, rows_per_rank: int, *, m: int, n: int, k: int,
+                   bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None, act: int = 0,
+                   d2: Optional[torch.Tensor] = None, beta: float = 1.0, max_ctas: int = 0, tile_n: int = 0,
+                   cta_pair: int = 0) -> torch.Tensor:
+    """Linear forward whose weight all-gather runs inside the GEMM kernel (``dtb_gemm_bf16_allgather``).
+
+    ``b_full`` is the local [n, k] weight buffer that receives the gathered rows; ``peer_shard_ptrs[r]`` is
+    rank r's [rows_per_rank, k] shard as mapped in this process."""
+    args = GemmArgs()
+    args.a, args.b, args.d = a.data_ptr(), b_full.data_ptr(), out.data_ptr()
+    args.d2 = d2.data_ptr() if d2 is not None else None
+    args.aux = aux.data_ptr() if aux is not None else None
+    args.bias = bias.data_ptr() if bias is not None else None
+    args.lda, args.ldb, args.ldd, args.ld_aux = k, k, n, n
+    args.m, args.n, args.k = m, n, k
+    args.batch_inner, args.batch_outer = 1, 1
+    args.d_fp32 = int(out.dtype == torch.float32)
+    args.aux_fp32 = int(aux is not None and aux.dtype == torch.float32)
+    args.bias_fp32 = int(bias is not None and bias.dtype == torch.float32)
+    args.act = act
+    args.alpha, args.beta = 1.0, beta
+    args.tile_n, args.cta_pair, args.max_ctas = tile_n, cta_pair, max_ctas
+    g = GatherArgs()
+    for r, ptr in enumerate(peer_shard_ptrs):
+        g.peer_shard[r] = ptr
+    g.flags = flags.data_ptr()
+    g.world, g.rank, g.rows_per_rank = len(peer_shard_ptrs), rank, rows_per_rank
+    _ok(lib().dtb_gemm_bf16_allgather(C.byref(args), C.byref(g), _stream()))
+    return out
+
+
 def linear_small_fwd(x, w, b, y):
     rows, in_f = x.shape
     _ok(lib().dtb_linear_small_fwd(_p(x), _p(w), _p(b), _p(y), rows, in_f, w.shape[0], _stream()))

@@ -364,6 +364,12 @@ class FSDPStrategy(DistributedStrategy):
         if self.comm is None:
             dev = torch.device("cuda", torch.cuda.current_device()) if self.is_gpu else torch.device("cpu")
             self.comm = make_communicator(dev)
+        if (getattr(self.comm, "supports_fused_step", False) and getattr(model, "supports_sharded_native", False)
+                and model.native_ready()):
+            # B200 path: all-gather fused into the forward GEMMs, reduce-scatter fused with the optimizer
+            from .sharded_native import NativeShardedModule
+
+            return NativeShardedModule(model, self.comm)
         return ShardedModule(model, self.comm, reshard_after_forward=self.reshard_after_forward)
 
     def save_checkpoint(self, model: nn.Module, state_dict: dict, path: str) -> None:
@@ -377,6 +383,10 @@ class FSDPStrategy(DistributedStrategy):
         return model, int(checkpoint["EPOCHS_RUN"])
 
     def build_optimizer(self, model: nn.Module, spec: OptimizerSpec) -> Any:
+        from .sharded_native import NativeShardedModule, NativeShardedOptimizer
+
+        if isinstance(model, NativeShardedModule):
+            return NativeShardedOptimizer(model, spec)
         if not isinstance(model, ShardedModule):
             raise TypeError("FSDPStrategy.build_optimizer expects the module returned by prepare_model")
         return ShardedOptimizer(model, spec, update_in_backward=True)

@@ -62,6 +62,25 @@ typedef struct dtb_gemm_args {
 } dtb_gemm_args;
 int dtb_gemm_bf16(const dtb_gemm_args* args, void* stream);
 
+/* All-gather fused into the GEMM that consumes the gathered weights (K6+K9: FSDP's all_gather_into_tensor
+ * followed by the Linear forward in the reference, /root/reference/src/dist_strategy/fsdp_strategy.py:20).
+ * B (= args->b, the local FULL weight matrix [N, K], K-major) is row-sharded over `world` ranks; rank r's
+ * shard [rows_per_rank, K] (same pitch ldb) is reachable at peer_shard[r] (symmetric heap, peer-mapped).
+ * Inside ONE kernel, extra warps of every CTA pull 16-row pieces of all shards over NVLink into B in the
+ * order the tiles need them (own rows first) and the TMA producer of a tile waits only for its own n-block,
+ * so the transfer overlaps the MMAs tile by tile and every byte crosses NVLink once.  After the call B holds
+ * the complete matrix (it is reused by the backward dgrad).  `flags`: dtb_gemm_allgather_flag_ints(N) ints of
+ * scratch, zeroed by the call.  A must be K-major; no batching.  The caller orders the call after the peers'
+ * shard updates (the reduce-scatter+optimizer kernel ends with a rank barrier). */
+#define DTB_MAX_RANKS 8
+typedef struct dtb_gather_args {
+  const void* peer_shard[DTB_MAX_RANKS];
+  int* flags;
+  int world, rank, rows_per_rank;
+} dtb_gather_args;
+size_t dtb_gemm_allgather_flag_ints(int n);
+int dtb_gemm_bf16_allgather(const dtb_gemm_args* args, const dtb_gather_args* gather, void* stream);
+
 /* Tiny-shape Linear for the reference's own model sizes (K=20,N=1; K=10,N=1): fp32 SIMT kernels. */
 int dtb_linear_small_fwd(const float* x, const float* w, const float* b, float* y, int rows, int in_f, int out_f,
                          void* stream);
@@ -170,7 +189,6 @@ int dtb_multi_tensor_adamw(const dtb_mt_args* args, float lr, float beta1, float
  * SM budget left to concurrently running GEMMs); bits 16..19 select the barrier channel (0..7).
  * Kernels that may run concurrently on different streams must use different channels; every rank
  * must issue the same sequence of collectives with the same arguments on a given channel. */
-#define DTB_MAX_RANKS 8
 #define DTB_SIGNAL_PAD_BYTES (64 * 1024)
 typedef struct dtb_comm {
   void* peers[DTB_MAX_RANKS];

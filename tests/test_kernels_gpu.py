@@ -397,3 +397,20 @@ def test_native_gpt2_step_matches_autograd():
         if err > 0.08 * scale + 2e-4:
             bad.append((name, err, scale))
     assert not bad, bad[:6]
+
+
+@pytest.mark.parametrize("m,n,k,cta_pair,tile_n", [(512, 1024, 512, 1, 128), (1024, 2048, 768, 2, 256),
+                                                    (384, 1600, 256, 1, 256)])
+def test_allgather_gemm_single_rank(m, n, k, cta_pair, tile_n):
+    """World size 1: the gather warps copy the (only) shard into the full matrix inside the GEMM kernel."""
+    x, shard = _bf16(m, k, seed=1), _bf16(n, k, scale=0.05, seed=2)
+    bias = _bf16(n, seed=3)
+    full = torch.full((n, k), float("nan"), dtype=torch.bfloat16, device=DEV)
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    flags = torch.ones(native.gemm_allgather_flag_ints(n), dtype=torch.int32, device=DEV) * 7   # call must zero them
+    native.gemm_allgather(x, full, out, [shard.data_ptr()], flags, 0, n, m=m, n=n, k=k, bias=bias,
+                          cta_pair=cta_pair, tile_n=tile_n)
+    torch.cuda.synchronize()
+    assert torch.equal(full, shard)
+    ref = x.float() @ shard.float().t() + bias.float()
+    assert torch.allclose(out.float(), ref, atol=0.08, rtol=2e-2)
