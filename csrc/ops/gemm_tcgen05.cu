@@ -436,7 +436,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
       }
       __syncwarp();
-      if (lane == 0) {
+      if (lane == 0 && r0 < p.N) {   // pieces past the last row do not count towards the block's quota
         __threadfence();
         atomicAdd(p.g_flags + n_blk, 1);
       }

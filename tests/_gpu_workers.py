@@ -169,11 +169,10 @@ def sharded_native(rank, world, port, out_dir):
                                                                                          weight_decay=0.1)
             opt = strategy.build_optimizer(wrapped, spec)
             torch.manual_seed(300)
-            ref = make(torch.float32).cuda()
+            ref = make(torch.bfloat16).float().cuda()        # rank 0's init
             full0 = wrapped.state_dict()
             for k, v in ref.state_dict().items():
-                assert torch.equal(full0[k].float(), v.to(torch.bfloat16).float().cpu()), k
-            ref.load_state_dict({k: v.float() for k, v in full0.items()})
+                assert torch.equal(full0[k].float(), v.cpu()), k
             ropt = (torch.optim.SGD(ref.parameters(), lr=0.05) if kind.endswith("sgd")
                     else torch.optim.AdamW(ref.parameters(), lr=2e-3, weight_decay=0.1))
             g = torch.Generator().manual_seed(11)
