@@ -252,11 +252,11 @@ class Trainer:
 
     # ------------------------------------------------------------------- steps
     def _loss(self, output: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        from .ops import functional as NF       # own loss kernels on GPU, PyTorch reference on CPU
+
         if self.config.loss == "mse":
-            return F.mse_loss(output.float(), targets.float())
-        if targets.dtype in (torch.int64, torch.int32):
-            return F.cross_entropy(output.float().view(-1, output.shape[-1]), targets.view(-1))
-        return F.cross_entropy(output.float(), targets.float())
+            return NF.mse_loss(output, targets)
+        return NF.cross_entropy(output, targets)
 
     def _run_batch(self, source: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
         if getattr(self.model, "native_step", False):
@@ -318,7 +318,9 @@ def build_model(model_cfg: Any) -> torch.nn.Module:
     name = model_cfg.get("name", "linear")
     dtype = _torch_dtype(model_cfg.get("dtype", "float32"))
     if name == "linear":
-        return torch.nn.Linear(model_cfg.input_size, model_cfg.output_size).to(dtype)
+        from .ops.functional import NativeLinear     # nn.Linear-compatible; own kernels when on a GPU
+
+        return NativeLinear(model_cfg.input_size, model_cfg.output_size).to(dtype)
     if name == "mlp":
         from .models.mlp import MLP
 

@@ -30,3 +30,17 @@ def test_native_sharded_strategy_matches_single_process(tmp_path):
     w = _world()
     mp.spawn(G.sharded_native, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(w))
+
+
+def test_trainer_minimum_slice_on_gpus(tmp_path):
+    w = 2
+    mp.spawn(G.trainer_gpu, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
+    a = [torch.load(tmp_path / f"res_a_rank{r}.pt", weights_only=False) for r in range(w)]
+    b = [torch.load(tmp_path / f"res_b_rank{r}.pt", weights_only=False) for r in range(w)]
+    assert a[0]["comm"] == "SymmComm" and a[0]["launches"] > 0          # native kernels, not a fallback
+    for k in a[0]["state"]:
+        assert torch.equal(a[0]["state"][k], a[1]["state"][k]) and torch.equal(b[0]["state"][k], b[1]["state"][k])
+    ckpt = torch.load(tmp_path / "snap.pt", weights_only=False)
+    assert ckpt["EPOCHS_RUN"] == 4 and list(ckpt["MODEL_STATE"]) == ["module.weight", "module.bias"]
+    log_b = (tmp_path / "run_b" / "train.log").read_text()
+    assert "Loading snapshot" in log_b and "Epoch 2 |" in log_b and "Epoch 1 |" not in log_b

@@ -414,3 +414,38 @@ def test_allgather_gemm_single_rank(m, n, k, cta_pair, tile_n):
     assert torch.equal(full, shard)
     ref = x.float() @ shard.float().t() + bias.float()
     assert torch.allclose(out.float(), ref, atol=0.08, rtol=2e-2)
+
+
+def test_functional_autograd_wrappers_match_torch():
+    from distributed_training_b200.ops import functional as NF
+
+    # bf16 Linear + GELU + LayerNorm + CE through autograd
+    torch.manual_seed(0)
+    x = _bf16(96, 256, seed=1).requires_grad_(True)
+    lin = NF.NativeLinear(256, 512).to(DEV).to(torch.bfloat16)
+    ln = torch.nn.LayerNorm(512).to(DEV).to(torch.bfloat16)
+    tgt = torch.randint(0, 512, (96,), device=DEV)
+    loss = NF.cross_entropy(NF.layer_norm(NF.gelu(lin(x)), ln.weight, ln.bias), tgt)
+    loss.backward()
+    xr = x.detach().float().requires_grad_(True)
+    w, b = lin.weight.detach().float().requires_grad_(True), lin.bias.detach().float().requires_grad_(True)
+    g, be = ln.weight.detach().float().requires_grad_(True), ln.bias.detach().float().requires_grad_(True)
+    ref = F.cross_entropy(F.layer_norm(F.gelu(F.linear(xr, w, b), approximate="tanh"), (512,), g, be), tgt)
+    ref.backward()
+    assert abs(float(loss) - float(ref.detach())) < 3e-2
+    for got, want in ((x.grad, xr.grad), (lin.weight.grad, w.grad), (lin.bias.grad, b.grad), (ln.weight.grad, g.grad)):
+        scale = want.abs().max().item() + 1e-6
+        assert (got.float() - want).abs().max().item() <= 0.08 * scale + 1e-4
+    # the reference's own toy model: fp32 Linear(20, 1) + MSE
+    toy = NF.NativeLinear(20, 1).to(DEV)
+    xs, ys = torch.randn(32, 20, device=DEV), torch.randn(32, 1, device=DEV)
+    l1 = NF.mse_loss(toy(xs), ys)
+    l1.backward()
+    wr, br = toy.weight.detach().clone().requires_grad_(True), toy.bias.detach().clone().requires_grad_(True)
+    l2 = F.mse_loss(F.linear(xs, wr, br), ys)
+    l2.backward()
+    assert torch.allclose(l1, l2, atol=1e-6)
+    assert torch.allclose(toy.weight.grad, wr.grad, atol=1e-5) and torch.allclose(toy.bias.grad, br.grad, atol=1e-5)
+    # soft-label CE, the reference trainer's objective (identically zero for one logit)
+    l3 = NF.cross_entropy(toy(xs), torch.rand(32, 1, device=DEV))
+    assert float(l3) == 0.0
