@@ -213,7 +213,7 @@ def sharded_native(rank, world, port, out_dir):
         dist.destroy_process_group()
 
 
-def trainer_gpu(rank, world, port, run_dir):
+def trainer_gpu(rank, world, port, run_dir, total, tag):
     """SURVEY §7.2 minimum slice: Hydra-configured trainer, toy Linear(20,1), DDP strategy on the peer-memory
     kernels (peer-store broadcast, one-shot fused all-reduce from the autograd hook, fused SGD), snapshot, resume."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
@@ -232,9 +232,8 @@ def trainer_gpu(rank, world, port, run_dir):
         captured["launches"] = native.launch_count()
         captured["comm"] = type(trainer._strategy.comm).__name__
 
-    for total, tag in ((3, "a"), (5, "b")):
-        overrides = [f"train.snapshot_path={snap}", "train.dataset_size=512", "train.batch_size=32",
-                     "train.dataset=teacher", "train.learning_rate=0.05", f"train.total_epochs={total}",
-                     "train.device=cuda", f"hydra.run.dir={run_dir}/run_{tag}"]
-        hc.run_job(lambda cfg: dt.run(cfg, before_teardown=grab), ROOT / "conf", "config", overrides)
-        torch.save(dict(captured), os.path.join(run_dir, f"res_{tag}_rank{rank}.pt"))
+    overrides = [f"train.snapshot_path={snap}", "train.dataset_size=512", "train.batch_size=32",
+                 "train.dataset=teacher", "train.learning_rate=0.05", f"train.total_epochs={total}",
+                 "train.device=cuda", f"hydra.run.dir={run_dir}/run_{tag}"]
+    hc.run_job(lambda cfg: dt.run(cfg, before_teardown=grab), ROOT / "conf", "config", overrides)
+    torch.save(dict(captured), os.path.join(run_dir, f"res_{tag}_rank{rank}.pt"))

@@ -32,9 +32,11 @@ def test_native_sharded_strategy_matches_single_process(tmp_path):
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(w))
 
 
+@pytest.mark.timeout(150)
 def test_trainer_minimum_slice_on_gpus(tmp_path):
     w = 2
-    mp.spawn(G.trainer_gpu, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
+    for total, tag in ((3, "a"), (5, "b")):      # second launch = a relaunch that resumes from the snapshot
+        mp.spawn(G.trainer_gpu, args=(w, free_port(), str(tmp_path), total, tag), nprocs=w, join=True)
     a = [torch.load(tmp_path / f"res_a_rank{r}.pt", weights_only=False) for r in range(w)]
     b = [torch.load(tmp_path / f"res_b_rank{r}.pt", weights_only=False) for r in range(w)]
     assert a[0]["comm"] == "SymmComm" and a[0]["launches"] > 0          # native kernels, not a fallback
