@@ -64,9 +64,10 @@ struct Config {
   static constexpr int B_ROWS = BN / CG;                   // B rows staged by one CTA
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (STAGE_BYTES >= 48 * 1024) ? 4 : 7;
+  static constexpr int STAGES = (STAGE_BYTES >= 48 * 1024) ? 4 : 6;
+  static constexpr int EPI_STAGE_BYTES = NUM_EPI_WARPS * 8192;   // per epilogue warp: 2 x [32 rows x 128 B]
   static constexpr int TMEM_COLS = 2 * BN;                 // two accumulator stages
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
   static_assert(TMEM_COLS <= 512, "TMEM has 512 columns");
   static_assert(TMEM_COLS == 128 || TMEM_COLS == 256 || TMEM_COLS == 512, "power of two");
 };
@@ -224,6 +225,109 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&raw)[
   }
 }
 
+// Epilogue for a 64-column group of one warp's 32 rows, staged through shared memory so that every global
+// access is a full 128-byte row segment (a thread owns a TMEM lane = an output row, so un-staged stores touch
+// 32 different cache lines per instruction, which dominates GEMMs with a short K such as the GPT-2 layers).
+// `st_out` / `st_in`: this warp's two [32 x 128 B] buffers; 16-byte chunk j of row r lives at chunk j ^ (r & 7).
+// Requirements (checked by the caller): bf16 D / aux, N % 8 == 0.
+__device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t taddr, int row_base, int colg,
+                                                      long long d_off, long long aux_off, uint8_t* st_out,
+                                                      uint8_t* st_in, int lane) {
+  const int sub = lane >> 3, seg = lane & 7;          // coalesced phase: 4 rows x 8 segments of 16 B per step
+  const bool has_aux = (p.aux != nullptr) && (p.act != 1);
+  if (has_aux) {
+    const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + aux_off;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int rl = it * 4 + sub, gr = row_base + rl, gc = colg + seg * 8;
+      uint4 val = make_uint4(0, 0, 0, 0);
+      if (gr < p.M && gc < p.N) val = *reinterpret_cast<const uint4*>(ap + static_cast<long long>(gr) * p.ld_aux + gc);
+      *reinterpret_cast<uint4*>(st_in + rl * 128 + ((seg ^ (rl & 7)) << 4)) = val;
+    }
+    __syncwarp();
+  }
+  const bool want_z = (p.act == 1) && (p.d2 != nullptr);
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    const int col0 = colg + half * 32;
+    if (col0 >= p.N) break;
+    uint32_t raw[32];
+    tmem_ld_32x32b_x32(taddr + half * 32, raw);
+    tmem_ld_wait();
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) * p.alpha;
+    if (p.bias != nullptr) {
+      if (p.bias_fp32) {
+        const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) v[j] += __ldg(b + j);
+      } else {
+        const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) v[j] += __bfloat162float(b[j]);
+      }
+    }
+    if (p.act == 1) {
+      if (want_z) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 o;
+          o.x = pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+          o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+          o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+          o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+          *reinterpret_cast<uint4*>(st_in + lane * 128 + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = gelu_tanh(v[j]);
+    } else if (has_aux) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint4 t = *reinterpret_cast<const uint4*>(st_in + lane * 128 + (((half * 4 + q) ^ (lane & 7)) << 4));
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h[e]);
+          if (p.act == 2) {
+            v[8 * q + 2 * e] *= gelu_tanh_grad(f.x);
+            v[8 * q + 2 * e + 1] *= gelu_tanh_grad(f.y);
+          } else {
+            v[8 * q + 2 * e] += p.beta * f.x;
+            v[8 * q + 2 * e + 1] += p.beta * f.y;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 o;
+      o.x = pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+      o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+      o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+      o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+      *reinterpret_cast<uint4*>(st_out + lane * 128 + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+    }
+  }
+  __syncwarp();
+  __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + d_off;
+  __nv_bfloat16* zp = reinterpret_cast<__nv_bfloat16*>(p.d2) + d_off;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int rl = it * 4 + sub, gr = row_base + rl, gc = colg + seg * 8;
+    if (gr < p.M && gc < p.N) {
+      const int so = rl * 128 + ((seg ^ (rl & 7)) << 4);
+      *reinterpret_cast<uint4*>(dp + static_cast<long long>(gr) * p.ldd + gc) = *reinterpret_cast<const uint4*>(st_out + so);
+      if (want_z)
+        *reinterpret_cast<uint4*>(zp + static_cast<long long>(gr) * p.ldd + gc) = *reinterpret_cast<const uint4*>(st_in + so);
+    }
+  }
+  __syncwarp();
+}
+
 constexpr int NUM_GATHER_WARPS = 2;
 
 template <int CG, int BN, int A_MN, int B_MN, bool GATHER = false>
@@ -236,7 +340,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;                                   // STAGES x A_BYTES
   uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;           // STAGES x B_BYTES
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint8_t* epi_stage = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_stage + Cfg::EPI_STAGE_BYTES);
   uint64_t* full_bar = bars;                  // [STAGES]
   uint64_t* empty_bar = bars + STAGES;        // [STAGES]
   uint64_t* tmem_full = bars + 2 * STAGES;    // [2]
@@ -457,12 +562,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      const bool staged = !p.d_fp32 && !(p.aux != nullptr && p.aux_fp32) && (p.N & 7) == 0;
+      if (staged) {
+        uint8_t* st_out = epi_stage + (warp - 2) * 8192;
+        const int row_base = row - lane;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t raw[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, raw);
-        tmem_ld_wait();
-        epilogue_chunk(p, raw, row, n0 + c * 32, d_off, aux_off);
+        for (int c2 = 0; c2 < BN / 64; ++c2) {
+          if (n0 + c2 * 64 >= p.N) break;
+          epilogue_group_staged(p, taddr + c2 * 64, row_base, n0 + c2 * 64, d_off, aux_off, st_out, st_out + 4096, lane);
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t raw[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, raw);
+          tmem_ld_wait();
+          epilogue_chunk(p, raw, row, n0 + c * 32, d_off, aux_off);
+        }
       }
       tcgen05_fence_before();
       __syncwarp();
