@@ -35,8 +35,8 @@ namespace comm {
 
 constexpr int MAX_BLOCKS = 128;      // barrier slots per channel
 constexpr int NUM_CHANNELS = 8;
-constexpr int THREADS = 256;      // 256 threads x <= 80 registers: a comm CTA fits on an SM NEXT TO a resident GEMM CTA
-constexpr int MIN_CTAS_PER_SM = 3; // launch-bounds hint that caps registers at 65536 / (256 * 3) = 85 -> 80
+constexpr int THREADS = 256;      // 256 threads x <= 64 registers: a comm CTA fits on an SM NEXT TO a resident GEMM CTA
+constexpr int MIN_CTAS_PER_SM = 4; // launch-bounds hint that caps registers at 65536 / (256 * 4) = 64, leaving 192 x 255 for the GEMM
 // signal pad layout (uint32 slots)
 constexpr int FLAG_SLOTS = NUM_CHANNELS * MAX_BLOCKS * DTB_MAX_RANKS;   // 8192
 constexpr int SEQ_BASE = FLAG_SLOTS;                                     // [channel][block] next sequence

@@ -13,6 +13,7 @@
 // Replaces the cuBLAS calls behind nn.Linear forward/backward in the reference
 // (/root/reference/src/distributed_trainer.py:162,164).
 #include <cuda.h>
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
@@ -54,6 +55,11 @@ struct Params {
   long long g_ldb;
   int g_world, g_rank, g_rows_per_rank;
   int g_rotate;            // n-blocks to rotate the visiting order by (rank * blocks_per_rank); -1 = off
+  int direct_epilogue;     // 1 = per-thread row stores (no shared-memory staging); DTB_GEMM_DIRECT_EPILOGUE=1
+  // ---- split-K: work unit = (tile, split); split s accumulates k-blocks [s*kb_per_split, ...) and writes its
+  // raw fp32 accumulators to ws[s][M][N]; splitk_reduce_kernel adds the slices in order and runs the epilogue.
+  int split_k, kb_per_split;
+  float* ws;
 };
 
 constexpr int GATHER_ROWS = 16;      // rows per gather piece
@@ -95,7 +101,45 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// v[0..32) += bias[col0 .. col0+32): four 16-byte loads when the whole chunk is in range and aligned
+__device__ __forceinline__ void add_bias32(const Params& p, float (&v)[32], int col0) {
+  if (p.bias_fp32) {
+    const float* b = reinterpret_cast<const float*>(p.bias) + col0;
+    if (col0 + 32 <= p.N && (reinterpret_cast<uintptr_t>(b) & 15) == 0) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(b) + q);
+        v[4 * q] += t.x; v[4 * q + 1] += t.y; v[4 * q + 2] += t.z; v[4 * q + 3] += t.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) v[j] += __ldg(b + j);
+    }
+  } else {
+    const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
+    if (col0 + 32 <= p.N && (reinterpret_cast<uintptr_t>(b) & 15) == 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint4 t = __ldg(reinterpret_cast<const uint4*>(b) + q);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h[e]);
+          v[8 * q + 2 * e] += f.x;
+          v[8 * q + 2 * e + 1] += f.y;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < p.N) v[j] += __bfloat162float(b[j]);
+    }
+  }
+}
+
 __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& bi, int& m_blk, int& n_blk) {
+  tile /= p.split_k;      // consecutive work units are the K-splits of one output tile
   const int per_batch = p.m_blocks * p.n_blocks;
   bi = tile / per_batch;
   int t = tile - bi * per_batch;
@@ -122,19 +166,7 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&raw)[
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) * p.alpha;
   const bool full = (col0 + 32 <= p.N);
 
-  if (p.bias != nullptr) {
-    if (p.bias_fp32) {
-      const float* b = reinterpret_cast<const float*>(p.bias) + col0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (full || col0 + j < p.N) v[j] += __ldg(b + j);
-    } else {
-      const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (full || col0 + j < p.N) v[j] += __bfloat162float(b[j]);
-    }
-  }
+  if (p.bias != nullptr) add_bias32(p, v, col0);
 
   if (p.act == 1) {
     if (p.d2 != nullptr) {
@@ -230,21 +262,34 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&raw)[
 // 32 different cache lines per instruction, which dominates GEMMs with a short K such as the GPT-2 layers).
 // `st_out` / `st_in`: this warp's two [32 x 128 B] buffers; 16-byte chunk j of row r lives at chunk j ^ (r & 7).
 // Requirements (checked by the caller): bf16 D / aux, N % 8 == 0.
+// Coalesced load of this warp's [32 rows x 64 cols] bf16 aux tile into registers (8 x 16 B per lane).
+__device__ __forceinline__ void load_aux_group(const Params& p, uint4 (&areg)[8], int row_base, int colg,
+                                               long long aux_off, int lane) {
+  const int sub = lane >> 3, seg = lane & 7;
+  const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + aux_off;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int gr = row_base + it * 4 + sub, gc = colg + seg * 8;
+    areg[it] = make_uint4(0, 0, 0, 0);
+    if (gr < p.M && gc < p.N) areg[it] = *reinterpret_cast<const uint4*>(ap + static_cast<long long>(gr) * p.ld_aux + gc);
+  }
+}
+
+// `areg` holds this group's aux tile (loaded one group ahead so its HBM latency hides behind the previous
+// group's math); on return it holds the tile of `next_colg` (if >= 0).
 __device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t taddr, int row_base, int colg,
                                                       long long d_off, long long aux_off, uint8_t* st_out,
-                                                      uint8_t* st_in, int lane) {
+                                                      uint8_t* st_in, int lane, uint4 (&areg)[8], int next_colg) {
   const int sub = lane >> 3, seg = lane & 7;          // coalesced phase: 4 rows x 8 segments of 16 B per step
   const bool has_aux = (p.aux != nullptr) && (p.act != 1);
   if (has_aux) {
-    const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + aux_off;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
-      const int rl = it * 4 + sub, gr = row_base + rl, gc = colg + seg * 8;
-      uint4 val = make_uint4(0, 0, 0, 0);
-      if (gr < p.M && gc < p.N) val = *reinterpret_cast<const uint4*>(ap + static_cast<long long>(gr) * p.ld_aux + gc);
-      *reinterpret_cast<uint4*>(st_in + rl * 128 + ((seg ^ (rl & 7)) << 4)) = val;
+      const int rl = it * 4 + sub;
+      *reinterpret_cast<uint4*>(st_in + rl * 128 + ((seg ^ (rl & 7)) << 4)) = areg[it];
     }
     __syncwarp();
+    if (next_colg >= 0) load_aux_group(p, areg, row_base, next_colg, aux_off, lane);
   }
   const bool want_z = (p.act == 1) && (p.d2 != nullptr);
 #pragma unroll 1
@@ -257,19 +302,7 @@ __device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t 
     float v[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) * p.alpha;
-    if (p.bias != nullptr) {
-      if (p.bias_fp32) {
-        const float* b = reinterpret_cast<const float*>(p.bias) + col0;
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (col0 + j < p.N) v[j] += __ldg(b + j);
-      } else {
-        const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.bias) + col0;
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (col0 + j < p.N) v[j] += __bfloat162float(b[j]);
-      }
-    }
+    if (p.bias != nullptr) add_bias32(p, v, col0);
     if (p.act == 1) {
       if (want_z) {
 #pragma unroll
@@ -354,7 +387,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   const bool leader = (cta_rank == 0);
   const int cluster_id = (CG == 2) ? (blockIdx.x >> 1) : blockIdx.x;
   const int num_clusters = (CG == 2) ? (gridDim.x >> 1) : gridDim.x;
-  const int num_tiles = p.m_blocks * p.n_blocks * p.batch;
+  const int num_tiles = p.m_blocks * p.n_blocks * p.batch * p.split_k;   // work units
   const int num_kb = (p.K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
@@ -403,7 +436,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
         asm volatile("fence.proxy.async.global;" ::: "memory");
       }
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const int kb_lo = (tile % p.split_k) * p.kb_per_split;
+      const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
+      for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
         uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
@@ -471,7 +506,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb_lo = (tile % p.split_k) * p.kb_per_split;
+        const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tcgen05_fence_after();
           const uint32_t a_lo = a_lo0 + static_cast<uint32_t>(stage) * (Cfg::A_BYTES >> 4);
@@ -481,14 +518,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t da = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * A_KSTEP16);
               const uint64_t db = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * B_KSTEP16);
-              umma_f16<CG>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+              umma_f16<CG>(tmem_d, da, db, idesc, (kb > kb_lo || k > 0) ? 1u : 0u);
             }
             if constexpr (CG == 1) {
               umma_commit(&empty_bar[stage]);
             } else {
               umma_commit_2sm(&empty_bar[stage], 0x3);
             }
-            if (kb == num_kb - 1) {
+            if (kb == kb_hi - 1) {
               if constexpr (CG == 1) {
                 umma_commit(&tmem_full[acc]);
               } else {
@@ -562,16 +599,41 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
-      const bool staged = !p.d_fp32 && !(p.aux != nullptr && p.aux_fp32) && (p.N & 7) == 0;
+      if (p.split_k > 1) {
+        // raw fp32 partial sums of this K-split: 128 contiguous bytes per thread and chunk
+        float* wrow = p.ws + (static_cast<long long>(tile % p.split_k) * p.M + row) * p.N + n0;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t raw[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, raw);
+          tmem_ld_wait();
+          const int col0 = n0 + c * 32;
+          if (row < p.M && col0 < p.N) {
+            if (col0 + 32 <= p.N) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                *reinterpret_cast<uint4*>(wrow + c * 32 + 4 * q) = make_uint4(raw[4 * q], raw[4 * q + 1], raw[4 * q + 2], raw[4 * q + 3]);
+            } else {
+              for (int j = 0; j < 32 && col0 + j < p.N; ++j) wrow[c * 32 + j] = __uint_as_float(raw[j]);
+            }
+          }
+        }
+      }
+      const bool staged = p.split_k == 1 && !p.direct_epilogue && !p.d_fp32 && !(p.aux != nullptr && p.aux_fp32) && (p.N & 7) == 0;
       if (staged) {
         uint8_t* st_out = epi_stage + (warp - 2) * 8192;
         const int row_base = row - lane;
+        const bool has_aux = (p.aux != nullptr) && (p.act != 1);
+        uint4 areg[8];
+        if (has_aux) load_aux_group(p, areg, row_base, n0, aux_off, lane);
 #pragma unroll 1
         for (int c2 = 0; c2 < BN / 64; ++c2) {
           if (n0 + c2 * 64 >= p.N) break;
-          epilogue_group_staged(p, taddr + c2 * 64, row_base, n0 + c2 * 64, d_off, aux_off, st_out, st_out + 4096, lane);
+          const int next = (c2 + 1 < BN / 64 && n0 + (c2 + 1) * 64 < p.N) ? n0 + (c2 + 1) * 64 : -1;
+          epilogue_group_staged(p, taddr + c2 * 64, row_base, n0 + c2 * 64, d_off, aux_off, st_out, st_out + 4096, lane,
+                                areg, next);
         }
-      } else {
+      } else if (p.split_k == 1) {
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           uint32_t raw[32];
@@ -603,6 +665,63 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   if (warp == 1) {
     tcgen05_fence_after();
     tmem_dealloc<CG>(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// Split-K finish: D = epilogue(alpha * sum_s ws[s]) for 8 consecutive columns per thread (N % 8 == 0).
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const Params p) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int n8 = p.N >> 3;
+  if (idx >= static_cast<long long>(p.M) * n8) return;
+  const int row = static_cast<int>(idx / n8), col = static_cast<int>(idx % n8) * 8;
+  float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int s = 0; s < p.split_k; ++s) {
+    const float* w = p.ws + (static_cast<long long>(s) * p.M + row) * p.N + col;
+    const float4 a = *reinterpret_cast<const float4*>(w), b = *reinterpret_cast<const float4*>(w + 4);
+    v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w; v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] *= p.alpha;
+  if (p.bias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      v[j] += p.bias_fp32 ? reinterpret_cast<const float*>(p.bias)[col + j]
+                          : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[col + j]);
+  }
+  if (p.act == 1) {
+    if (p.d2 != nullptr) {
+      uint4 o = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.d2) + static_cast<long long>(row) * p.ldd + col) = o;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+  } else if (p.aux != nullptr) {
+    float a[8];
+    if (p.aux_fp32) {
+      const float* ap = reinterpret_cast<const float*>(p.aux) + static_cast<long long>(row) * p.ld_aux + col;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] = ap[j];
+    } else {
+      const uint4 t = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
+                                                      static_cast<long long>(row) * p.ld_aux + col);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h[e]);
+        a[2 * e] = f.x;
+        a[2 * e + 1] = f.y;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (p.act == 2) ? v[j] * gelu_tanh_grad(a[j]) : v[j] + p.beta * a[j];
+  }
+  if (p.d_fp32) {
+    float* dp = reinterpret_cast<float*>(p.d) + static_cast<long long>(row) * p.ldd + col;
+    *reinterpret_cast<float4*>(dp) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(dp + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  } else {
+    uint4 o = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<long long>(row) * p.ldd + col) = o;
   }
 }
 
@@ -697,17 +816,45 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   // tile selection: pair mode for big problems; 128-wide N tiles when 256 would leave SMs idle
   int cg = a->cta_pair;
   int bn = a->tile_n;
+  const int num_kb_total = (a->k + BK - 1) / BK;
+  // split-K needs a workspace, a plain (unbatched, non-gather) problem and 16-byte-granular rows
+  const bool can_split = g == nullptr && bi * bo == 1 && a->workspace != nullptr && a->split_k != 1 &&
+                         (a->n % 8) == 0 && num_kb_total >= 8;
   if (bn == 0) {
     const long long tiles256 = 1LL * ((a->m + 127) / 128) * ((a->n + 255) / 256) * bi * bo;
     bn = (a->n > 128 && tiles256 >= sms) ? 256 : 128;
     if (a->n <= 128) bn = 128;
+    // few output tiles but a long K: 256-wide tiles (half the operand traffic per FLOP) and split K instead
+    if (can_split && a->cta_pair != 1 && a->m >= 256 && a->n >= 256) bn = 256;
   }
   DTB_REQUIRE(bn == 128 || bn == 256, "dtb_gemm_bf16: tile_n must be 128 or 256");
   if (cg == 0) {
     const long long tiles_pair = 1LL * ((a->m + 255) / 256) * ((a->n + bn - 1) / bn) * bi * bo;
-    cg = (bn == 256 && a->m >= 256 && tiles_pair >= sms / 2) ? 2 : 1;
+    cg = (bn == 256 && a->m >= 256 && (tiles_pair >= sms / 2 || can_split)) ? 2 : 1;
   }
   DTB_REQUIRE(cg == 1 || (cg == 2 && bn == 256), "dtb_gemm_bf16: cta_pair=2 requires tile_n=256");
+
+  int split = 1, kb_per_split = num_kb_total;
+  if (can_split) {
+    const long long units = 1LL * ((a->m + BM * cg - 1) / (BM * cg)) * ((a->n + bn - 1) / bn);
+    const long long slots = cg == 2 ? (sms / 2) : sms;
+    // cost in k-block times: waves * (k-blocks per unit + pipeline fill / epilogue), plus the reduce pass
+    const double fill = 6.0, reduce_cost = 8.0;
+    double best = static_cast<double>((units + slots - 1) / slots) * (num_kb_total + fill);
+    const int max_split = a->split_k > 1 ? a->split_k : 8;
+    for (int sk = 2; sk <= max_split; ++sk) {
+      const int kbps = (num_kb_total + sk - 1) / sk;
+      if (kbps < 4) break;
+      const int eff = (num_kb_total + kbps - 1) / kbps;
+      if (static_cast<long long>(eff) * a->m * a->n * 4 > a->workspace_bytes) break;
+      const double cost = static_cast<double>((units * eff + slots - 1) / slots) * (kbps + fill) + reduce_cost;
+      if (cost < best * 0.9 || (a->split_k > 1 && sk == a->split_k)) {
+        best = cost;
+        split = eff;
+        kb_per_split = kbps;
+      }
+    }
+  }
 
   Params p = {};
   p.M = a->m; p.N = a->n; p.K = a->k;
@@ -730,6 +877,13 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   p.lbo_b = a->dbg_lbo_b ? a->dbg_lbo_b : (a->b_mn_major ? 8192u : 16u);
   p.sbo_b = a->dbg_sbo_b ? a->dbg_sbo_b : 1024u;
   p.g_rotate = -1;
+  p.split_k = split;
+  p.kb_per_split = kb_per_split;
+  p.ws = static_cast<float*>(a->workspace);
+  {
+    static const int direct = [] { const char* e = getenv("DTB_GEMM_DIRECT_EPILOGUE"); return (e && e[0] == '1') ? 1 : 0; }();
+    p.direct_epilogue = direct;
+  }
   if (g != nullptr) {
     DTB_REQUIRE(!a->a_mn_major && !a->b_mn_major && bi * bo == 1,
                 "dtb_gemm_bf16_allgather: forward layout only (A, B K-major, no batch)");
@@ -761,7 +915,7 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
                        bn / cg))
     return 1;
 
-  const long long tiles = 1LL * p.m_blocks * p.n_blocks * p.batch;
+  const long long tiles = 1LL * p.m_blocks * p.n_blocks * p.batch * p.split_k;
   int max_ctas = a->max_ctas > 0 ? (a->max_ctas < sms ? a->max_ctas : sms) : sms;
   int grid;
   if (cg == 2) {
@@ -778,9 +932,15 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
     if (bn == 256) return launch<1, 256, 0, 0, true>(ma, mb, p, grid, s);
     return launch<1, 128, 0, 0, true>(ma, mb, p, grid, s);
   }
-  if (cg == 2) return dispatch_major<2, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
-  if (bn == 256) return dispatch_major<1, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
-  return dispatch_major<1, 128>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+  int rc;
+  if (cg == 2) rc = dispatch_major<2, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+  else if (bn == 256) rc = dispatch_major<1, 256>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+  else rc = dispatch_major<1, 128>(ma, mb, p, a->a_mn_major, a->b_mn_major, grid, s);
+  if (rc != 0 || p.split_k == 1) return rc;
+  const long long vecs = static_cast<long long>(p.M) * (p.N / 8);
+  splitk_reduce_kernel<<<static_cast<unsigned>((vecs + 255) / 256), 256, 0, s>>>(p);
+  DTB_LAUNCH_OK();
+  return 0;
 }
 
 extern "C" int dtb_gemm_bf16(const dtb_gemm_args* a, void* stream) { return gemm_impl(a, nullptr, stream); }

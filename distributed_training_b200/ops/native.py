@@ -40,6 +40,7 @@ class GemmArgs(C.Structure):
         ("alpha", C.c_float), ("beta", C.c_float),
         ("tile_n", C.c_int), ("cta_pair", C.c_int), ("max_ctas", C.c_int),
         ("dbg_lbo_a", C.c_uint), ("dbg_sbo_a", C.c_uint), ("dbg_lbo_b", C.c_uint), ("dbg_sbo_b", C.c_uint),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_longlong), ("split_k", C.c_int),
     ]
 
 
@@ -121,6 +122,18 @@ def reset_launch_count() -> None:
 # ---------------------------------------------------------------------------
 # GEMM
 # ---------------------------------------------------------------------------
+_GEMM_WS = {}
+
+
+def _gemm_workspace(device: torch.device) -> torch.Tensor:
+    """Per-device fp32 scratch for split-K partial sums (64 MiB: 8 slices of a 1024 x 2048 output)."""
+    ws = _GEMM_WS.get(device)
+    if ws is None:
+        ws = torch.empty(16 << 20, dtype=torch.float32, device=device)
+        _GEMM_WS[device] = ws
+    return ws
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, m: int, n: int, k: int,
          a_mn: bool = False, b_mn: bool = False, lda: Optional[int] = None, ldb: Optional[int] = None,
          ldd: Optional[int] = None, bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
@@ -128,7 +141,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, m: int, n: int,
          d2: Optional[torch.Tensor] = None, batch: Tuple[int, int] = (1, 1),
          a_strides: Tuple[int, int] = (0, 0), b_strides: Tuple[int, int] = (0, 0),
          d_strides: Tuple[int, int] = (0, 0), aux_strides: Tuple[int, int] = (0, 0),
-         tile_n: int = 0, cta_pair: int = 0, max_ctas: int = 0, dbg: Tuple[int, int, int, int] = (0, 0, 0, 0)) -> torch.Tensor:
+         tile_n: int = 0, cta_pair: int = 0, max_ctas: int = 0, dbg: Tuple[int, int, int, int] = (0, 0, 0, 0),
+         split_k: int = 0) -> torch.Tensor:
     """``out[m,n] = epilogue(alpha * sum_k A(m,k) B(n,k))`` — see ``dtb_gemm_bf16`` in the header.
 
     ``a``/``b`` are bf16; layouts are described by ``*_mn`` and the leading
@@ -158,6 +172,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, m: int, n: int,
     args.alpha, args.beta = alpha, beta
     args.tile_n, args.cta_pair, args.max_ctas = tile_n, cta_pair, max_ctas
     args.dbg_lbo_a, args.dbg_sbo_a, args.dbg_lbo_b, args.dbg_sbo_b = dbg
+    if split_k != 1 and batch == (1, 1) and k >= 512:
+        ws = _gemm_workspace(a.device)
+        args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+    args.split_k = split_k
     _ok(lib().dtb_gemm_bf16(C.byref(args), _stream()))
     return out
 

@@ -59,6 +59,13 @@ typedef struct dtb_gemm_args {
   int cta_pair;          /* 0 = auto, 1 = force 1-CTA MMA, 2 = force cta_group::2 */
   int max_ctas;          /* 0 = all SMs; otherwise cap the persistent grid (leave SMs to a comm kernel) */
   unsigned dbg_lbo_a, dbg_sbo_a, dbg_lbo_b, dbg_sbo_b;   /* 0 = default; bring-up overrides */
+  /* split-K (problems with few output tiles and a long K, e.g. transformer wgrads): fp32 partial sums of the
+   * K slices go through `workspace` and a second kernel adds them in slice order and applies the epilogue.
+   * workspace == NULL or split_k == 1 disables it; split_k == 0 lets the library choose (cost model);
+   * split_k >= 2 forces that many slices.  Needs split * m * n * 4 bytes. */
+  void* workspace;
+  long long workspace_bytes;
+  int split_k;
 } dtb_gemm_args;
 int dtb_gemm_bf16(const dtb_gemm_args* args, void* stream);
 

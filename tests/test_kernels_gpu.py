@@ -449,3 +449,21 @@ def test_functional_autograd_wrappers_match_torch():
     # soft-label CE, the reference trainer's objective (identically zero for one logit)
     l3 = NF.cross_entropy(toy(xs), torch.rand(32, 1, device=DEV))
     assert float(l3) == 0.0
+
+
+@pytest.mark.parametrize("split", [0, 2, 5])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, True)])
+def test_gemm_split_k(split, a_mn, b_mn):
+    """Few output tiles, long K (transformer wgrad shape): partial sums through the workspace + reduce kernel."""
+    m, n, k = 768, 512, 4096
+    a = _bf16(*((k, m) if a_mn else (m, k)), scale=0.5, seed=1)
+    b = _bf16(*((k, n) if b_mn else (n, k)), scale=0.5, seed=2)
+    bias, res = _bf16(n, seed=3), _bf16(m, n, seed=4)
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    native.gemm(a, b, out, m=m, n=n, k=k, a_mn=a_mn, b_mn=b_mn, bias=bias, aux=res, beta=0.5, alpha=0.25, split_k=split)
+    ref = 0.25 * _gemm_ref(a, b, a_mn, b_mn) + bias.float() + 0.5 * res.float()
+    assert torch.allclose(out.float(), ref, atol=0.15, rtol=2e-2), (out.float() - ref).abs().max()
+    # split 1 (disabled) must agree with the split result to bf16 rounding
+    one = torch.empty_like(out)
+    native.gemm(a, b, one, m=m, n=n, k=k, a_mn=a_mn, b_mn=b_mn, bias=bias, aux=res, beta=0.5, alpha=0.25, split_k=1)
+    assert torch.allclose(out.float(), one.float(), atol=0.13, rtol=2e-2)
