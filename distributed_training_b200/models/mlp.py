@@ -136,6 +136,15 @@ class MLP(nn.Module):
                             max_ctas=max_ctas)
                 if on_updated is not None:
                     on_updated([layer.weight])
+            elif i == 0 and getattr(grad_sink, "tail_chunks", lambda p: 1)(layer.weight) > 1:
+                # the last wgrad of backward: produce (and reduce) it in row chunks so that only the final
+                # chunk's reduction is exposed
+                nch = grad_sink.tail_chunks(layer.weight)
+                gw, per = grad_of(layer.weight), out_f // nch
+                for c in range(nch):
+                    native.gemm(dz[:, c * per:], h_in, gw[c * per:], m=per, n=in_f, k=rows, a_mn=True, b_mn=True,
+                                lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
+                    grad_sink.mark_ready_chunk(layer.weight, c, nch)
             else:
                 # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major), straight into the gradient bucket
                 native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,

@@ -111,6 +111,7 @@ class ReplicatedModule(nn.Module):
         self.attach_grad_views()
         self._callback_queued = False
         self._in_manual_step = False
+        self._chunk_works: List[Work] = []
         #: seconds (CPU) or milliseconds of stream stall (CUDA) the last step spent
         #: waiting for gradient communication after backward had finished
         self.last_exposed_comm_ms = 0.0
@@ -212,6 +213,42 @@ class ReplicatedModule(nn.Module):
         i = self._index_of[id(param)]
         self._count_down(self._bucket_of[i], i)
 
+    #: weights smaller than this are reduced in one piece even when they end backward
+    TAIL_CHUNK_MIN_BYTES = 32 << 20
+
+    def tail_chunks(self, param: nn.Parameter) -> int:
+        """How many row chunks the *last* weight gradient of backward should be produced in.  Its reduction
+        cannot overlap anything, so cutting it in pieces lets all but the last piece hide behind the
+        remaining wgrad GEMMs."""
+        i = self._index_of[id(param)]
+        bucket = self._bucket_of[i]
+        if self.comm.world_size == 1 or bucket.expected != 1 or param.dim() != 2 or param.shape[0] % 4:
+            return 1
+        return 4 if bucket.plan.nbytes >= self.TAIL_CHUNK_MIN_BYTES else 1
+
+    def mark_ready_chunk(self, param: nn.Parameter, chunk: int, n_chunks: int) -> None:
+        """Rows ``[chunk, chunk+1) * rows/n_chunks`` of ``param``'s gradient are final: reduce just that slice
+        (the parameter must own its bucket, see :meth:`tail_chunks`)."""
+        if not self.require_backward_grad_sync:
+            return
+        i = self._index_of[id(param)]
+        bucket = self._bucket_of[i]
+        assert bucket.expected == 1 and bucket.plan.slots[0].offset == 0
+        per = param.numel() // n_chunks
+        lo, hi = chunk * per, (chunk + 1) * per
+        hyper = self._fused_sgd_hyper() if self._in_manual_step else None
+        if hyper is not None and bucket.param_buffer is not None and bucket.plan.dtype == torch.bfloat16:
+            work = self.comm.all_reduce_sgd_(bucket.buffer[lo:hi], bucket.param_buffer[lo:hi], *hyper)
+            if chunk == n_chunks - 1:
+                self._optimizer.mark_updated([param])
+        else:
+            work = self.comm.all_reduce_avg_(bucket.buffer[lo:hi])
+        self._chunk_works.append(work)
+        if chunk == n_chunks - 1:
+            bucket.ready.add(i)
+            bucket.pending = 0
+            bucket.launched = True
+
     def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, **kwargs: Any) -> torch.Tensor:
         """One fused forward+backward of a native model with overlapped reduction."""
         if not hasattr(self.module, "forward_backward"):
@@ -247,6 +284,9 @@ class ReplicatedModule(nn.Module):
         for bucket in self.buckets:
             if bucket.work is not None:
                 bucket.work.wait()
+        for work in self._chunk_works:
+            work.wait()
+        self._chunk_works.clear()
         if cuda:
             stop.record()
             self._stall_events = (start, stop)
@@ -288,10 +328,11 @@ class DDPStrategy(DistributedStrategy):
     ``DDPStrategy(local_rank, is_gpu)`` (/root/reference/src/dist_strategy/ddp_strategy.py:10-13)."""
 
     def __init__(self, local_rank: int = 0, is_gpu: bool = False, bucket_cap_mb: float = 25.0,
-                 comm: Optional[Communicator] = None) -> None:
+                 comm: Optional[Communicator] = None, first_bucket_mb: float = 1.0) -> None:
         self.local_rank = local_rank
         self.is_gpu = is_gpu
         self.bucket_cap_mb = bucket_cap_mb
+        self.first_bucket_mb = first_bucket_mb
         self.comm = comm
 
     def _device(self, device: Any) -> torch.device:
@@ -303,7 +344,8 @@ class DDPStrategy(DistributedStrategy):
     def prepare_model(self, model: nn.Module, device: Any) -> nn.Module:
         if self.comm is None:
             self.comm = make_communicator(self._device(device))
-        return ReplicatedModule(model, self.comm, bucket_cap_mb=self.bucket_cap_mb)
+        return ReplicatedModule(model, self.comm, bucket_cap_mb=self.bucket_cap_mb,
+                                first_bucket_mb=self.first_bucket_mb)
 
     def save_checkpoint(self, model: nn.Module, state_dict: dict, path: str) -> None:
         atomic_torch_save(state_dict, path)

@@ -92,11 +92,16 @@ def ddp_native(rank, world, port, out_dir):
     _init(rank, world, port)
     strategy = DDPStrategy(rank, True)
     try:
-      for fused in (False, True):
+      for fused in (False, True, "chunked"):
+        if fused == "chunked":   # every parameter in its own bucket + chunked reduction of the last wgrad
+            strategy = DDPStrategy(rank, True, comm=strategy.comm, bucket_cap_mb=0.01, first_bucket_mb=0.001)
         torch.manual_seed(100 + rank)                        # rank-dependent init: must be broadcast
         model = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16).cuda()
         wrapped = strategy.prepare_model(model, rank)
         assert wrapped.native_step
+        if fused == "chunked":
+            wrapped.TAIL_CHUNK_MIN_BYTES = 0
+            assert wrapped.tail_chunks(model.layers[0].weight) == 4
         opt = strategy.build_optimizer(wrapped, OptimizerSpec("sgd", lr=0.05, weight_decay=0.01))
         if fused:
             wrapped.attach_optimizer(opt)                    # gradient all-reduce + SGD in one kernel
