@@ -88,7 +88,9 @@ class SymmComm(Communicator):
         if self.world_size not in (1, 2, 4, 8):
             raise ValueError(f"SymmComm supports 1, 2, 4 or 8 ranks per node, got {self.world_size}")
         self.segment_bytes = int(segment_bytes)
-        self.comm_ctas = comm_ctas
+        # CTA budget of a collective (0 = library default of 64): with 2 ranks each rank moves half of every
+        # buffer, so more CTAs are needed to keep enough bytes in flight
+        self.comm_ctas = comm_ctas if comm_ctas else (128 if self.world_size == 2 else 0)
         self.segments: List[Segment] = []
         self._owner_of: Dict[int, Tuple[Segment, int]] = {}   # storage data_ptr -> (segment, offset)
         self.stream = torch.cuda.Stream(self.device, priority=-1) if overlap_stream else None
