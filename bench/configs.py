@@ -27,6 +27,9 @@ def main():
     ap.add_argument("--optimizer", default=None)
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--layers", type=int, default=0)
+    ap.add_argument("--ref-loss", action="store_true",
+                    help="torch arm: F.cross_entropy(output[B,V,T], targets) exactly as the reference Trainer calls it "
+                         "(default: flat fp32 logits, the layout the product model uses)")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ns = ap.parse_args()
@@ -100,7 +103,12 @@ def main():
 
         def step(i):
             opt.zero_grad()
-            torch.nn.functional.cross_entropy(wrapped(x), y).backward()
+            out = wrapped(x)
+            if is_mlp or ns.ref_loss:
+                loss = torch.nn.functional.cross_entropy(out, y)
+            else:       # [B, V, T] -> [B*T, V] fp32
+                loss = torch.nn.functional.cross_entropy(out.transpose(1, 2).float().reshape(-1, out.shape[1]), y.view(-1))
+            loss.backward()
             opt.step()
 
         for i in range(ns.warmup):
