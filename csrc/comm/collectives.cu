@@ -23,6 +23,7 @@
 // Reference call sites: dist.broadcast / dist.all_reduce in
 // /root/reference/src/playground/ddp_script.py:120-121,149-154 and the implicit
 // NCCL collectives of torch DDP / FSDP (ddp_strategy.py:18, fsdp_strategy.py:20).
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
@@ -213,6 +214,89 @@ allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec, const SgdAr
   store_seq(x, seq);
 }
 
+// 32-byte accesses with "no L1 allocate, evict-first in L2" (LDG/STG.E.NA.EFL2.256): half the instructions of the
+// 16-byte path, and the gradient stream does not push the concurrently running GEMM's operands out of L2.
+struct V8 {
+  uint32_t w[8];
+};
+__device__ __forceinline__ V8 ld256_stream(const void* p) {
+  V8 r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void st256_stream(void* p, const V8& v) {
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v.w[0]),
+               "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3]), "r"(v.w[4]), "r"(v.w[5]), "r"(v.w[6]), "r"(v.w[7])
+               : "memory");
+}
+
+// bf16 two-shot mean (optionally fused with SGD) on 32-byte vectors; same semantics and reduction order as
+// allreduce_twoshot_kernel.  Peers are read four at a time to stay within the 64-register budget.
+template <int W, bool SGD>
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
+allreduce_twoshot256_kernel(const Ctx x, size_t offset, long long nvec32, const SgdArgs sgd) {
+  constexpr int G = W < 4 ? W : 4;          // loads in flight per batch
+  constexpr int U = W <= 2 ? 2 : 1;
+  uint32_t seq = load_seq(x);
+  rank_barrier(x, seq);
+  const long long lo = nvec32 * x.c.rank / W, hi = nvec32 * (x.c.rank + 1) / W;
+  const float scale = 1.f / W;
+  const long long stride = static_cast<long long>(gridDim.x) * THREADS;
+  for (long long v0 = lo + static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v0 < hi; v0 += stride * U) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= hi) break;
+      const size_t off = offset + static_cast<size_t>(v) * 32;
+      float acc[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+#pragma unroll
+      for (int r0 = 0; r0 < W; r0 += G) {
+        V8 raw[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) raw[g] = ld256_stream(static_cast<const uint8_t*>(x.c.peers[r0 + g]) + off);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw[g].w[j]));
+            acc[2 * j] += f.x;
+            acc[2 * j + 1] += f.y;
+          }
+        }
+      }
+      size_t dst = off;
+      if (SGD) {
+        dst = sgd.param_offset + static_cast<size_t>(v) * 32;
+        const V8 praw = ld256_stream(static_cast<const uint8_t*>(x.c.peers[x.c.rank]) + dst);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&praw.w[j]));
+          acc[2 * j] = f.x * sgd.decay - sgd.lr * (acc[2 * j] * scale);
+          acc[2 * j + 1] = f.y * sgd.decay - sgd.lr * (acc[2 * j + 1] * scale);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[j] *= scale;
+      }
+      V8 out;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+        out.w[j] = *reinterpret_cast<uint32_t*>(&h);
+      }
+#pragma unroll
+      for (int r = 0; r < W; ++r) st256_stream(static_cast<uint8_t*>(x.c.peers[r]) + dst, out);
+    }
+  }
+  rank_barrier(x, seq);
+  store_seq(x, seq);
+}
+
 // One-shot in-place mean for small buffers: each rank reduces the whole buffer into
 // registers, all ranks meet (nobody may overwrite data a peer still reads), then store.
 template <bool FP32, int W, int PER_THREAD>
@@ -353,6 +437,12 @@ static int pick_grid(long long nvec, int max_ctas, int dflt) {
   return static_cast<int>(need < cap ? need : cap);
 }
 
+// DTB_COMM_WIDE=0 falls back to the 16-byte kernels
+static bool wide_enabled() {
+  static const bool on = [] { const char* e = getenv("DTB_COMM_WIDE"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 static int check(const dtb_comm* c, int channel) {
   DTB_REQUIRE(c != nullptr && c->world >= 1 && c->world <= DTB_MAX_RANKS && c->rank >= 0 && c->rank < c->world,
               "dtb_comm: bad communicator");
@@ -425,8 +515,10 @@ extern "C" int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long lo
   } else {
     const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 64);
     const SgdArgs none = {0, 0.f, 1.f};
+    const bool wide = dtype == 0 && offset % 32 == 0 && (n * esize) % 32 == 0 && wide_enabled();
     DISPATCH_W(c->world, {
       if (dtype == 1) allreduce_twoshot_kernel<true, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
+      else if (wide) allreduce_twoshot256_kernel<W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec / 2, none);
       else allreduce_twoshot_kernel<false, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
     });
   }
@@ -445,7 +537,11 @@ extern "C" int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, si
   const int grid = pick_grid(nvec / c->world + 1, ctas_of(max_ctas), 64);
   const SgdArgs sgd = {param_offset, lr, 1.f - lr * weight_decay};
   auto s = static_cast<cudaStream_t>(stream);
-  DISPATCH_W(c->world, { allreduce_twoshot_kernel<false, W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, sgd); });
+  const bool wide = grad_offset % 32 == 0 && param_offset % 32 == 0 && (n * 2) % 32 == 0 && wide_enabled();
+  DISPATCH_W(c->world, {
+    if (wide) allreduce_twoshot256_kernel<W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec / 2, sgd);
+    else allreduce_twoshot_kernel<false, W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, sgd);
+  });
   DTB_LAUNCH_OK();
   return 0;
 }
