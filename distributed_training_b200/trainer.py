@@ -40,6 +40,7 @@ from .data import (LinearTeacherDataset, MyTrainDataset, ShardedLoader, ShardedS
 from .parallel.ddp import DDPStrategy
 from .parallel.sharded import FSDPStrategy
 from .parallel.strategy import DistributedStrategy, OptimizerSpec
+from .utils.tracing import nvtx_range
 
 try:  # real Hydra when present, the bundled shim otherwise
     import hydra as _hydra  # type: ignore
@@ -261,13 +262,17 @@ class Trainer:
     def _run_batch(self, source: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
         if getattr(self.model, "native_step", False):
             # native kernels overwrite their gradient buffers: no zero_grad pass over the parameters
-            loss = self.model.forward_backward(source, targets, loss=self.config.loss)
+            with nvtx_range("forward_backward"):
+                loss = self.model.forward_backward(source, targets, loss=self.config.loss)
         else:
             self.optimizer.zero_grad()
-            output = self.model(source)
-            loss = self._loss(output, targets)
-            loss.backward()
-        self.optimizer.step()
+            with nvtx_range("forward"):
+                output = self.model(source)
+                loss = self._loss(output, targets)
+            with nvtx_range("backward"):
+                loss.backward()
+        with nvtx_range("optimizer"):
+            self.optimizer.step()
         self.last_loss = loss.detach()
         return self.last_loss
 
