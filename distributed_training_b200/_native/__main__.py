@@ -2,4 +2,10 @@ import sys
 
 from . import build
 
-print(build(force="--force" in sys.argv, verbose=True))
+
+def main() -> None:
+    print(build(force="--force" in sys.argv, verbose=True))
+
+
+if __name__ == "__main__":
+    main()

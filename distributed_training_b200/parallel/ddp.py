@@ -26,6 +26,7 @@ peer-memory kernels on B200 (``SymmComm``).
 from __future__ import annotations
 
 import contextlib
+import zlib
 import logging
 import time
 from typing import Any, Dict, Iterator, List, Optional, Tuple
@@ -81,6 +82,7 @@ class ReplicatedModule(nn.Module):
         self._params: List[nn.Parameter] = [p for p in module.parameters() if p.requires_grad]
         self._index_of: Dict[int, int] = {id(p): i for i, p in enumerate(self._params)}
         if init_sync:
+            self.verify_replicas()
             self.sync_parameters()
 
         plans = plan_buckets(self._params, int(bucket_cap_mb * (1 << 20)),
@@ -118,6 +120,20 @@ class ReplicatedModule(nn.Module):
         self._stall_events: Optional[Tuple[Any, Any]] = None
 
     # ------------------------------------------------------------------ setup
+    def verify_replicas(self) -> None:
+        """Fail fast if ranks wrapped different architectures (torch's ``_verify_param_shape_across_processes``,
+        SURVEY N1): a CRC of every parameter's name, shape and dtype must agree on all ranks."""
+        if self.comm.world_size == 1:
+            return
+        desc = ";".join(f"{n}:{tuple(p.shape)}:{p.dtype}" for n, p in self.module.named_parameters())
+        crc = float(zlib.crc32(desc.encode()))           # < 2**32, exact in float64
+        hi = self.comm.all_reduce_max_scalar(crc)
+        lo = -self.comm.all_reduce_max_scalar(-crc)
+        if hi != lo:
+            raise RuntimeError(
+                f"rank {self.comm.rank}: replicas disagree on parameter names/shapes/dtypes "
+                f"(fingerprint {int(crc):#x}, range {int(lo):#x}..{int(hi):#x})")
+
     def sync_parameters(self, src: int = 0) -> None:
         """Broadcast rank ``src``'s parameters and buffers (DDP init sync)."""
         tensors = [p.data for p in self.module.parameters()] + [b.data for b in self.module.buffers()]

@@ -129,3 +129,20 @@ def sharded_parity(rank, world, port, out_dir):
         torch.save({"ok": True}, os.path.join(out_dir, f"ok{rank}.pt"))
     finally:
         dist.destroy_process_group()
+
+
+def mismatched_replicas(rank, world, port, out_dir):
+    """Ranks wrap different architectures: the wrapper must refuse on EVERY rank (torch's shape verification)."""
+    from distributed_training_b200.parallel.comm import TorchDistComm
+    from distributed_training_b200.parallel.ddp import ReplicatedModule
+
+    init(rank, world, port)
+    try:
+        model = nn.Linear(20, 1 + rank)
+        try:
+            ReplicatedModule(model, TorchDistComm(torch.device("cpu")))
+        except RuntimeError as err:
+            assert "disagree" in str(err)
+            torch.save({"ok": True}, os.path.join(out_dir, f"ok{rank}.pt"))
+    finally:
+        dist.destroy_process_group()

@@ -15,6 +15,11 @@ def test_replicated_module_matches_torch_ddp(world, tmp_path):
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(world))
 
 
+def test_mismatched_replicas_are_rejected(tmp_path):
+    mp.spawn(W.mismatched_replicas, args=(2, free_port(), str(tmp_path)), nprocs=2, join=True)
+    assert all((tmp_path / f"ok{r}.pt").exists() for r in range(2))
+
+
 def test_sharded_strategy_matches_single_process(tmp_path):
     mp.spawn(W.sharded_parity, args=(2, free_port(), str(tmp_path)), nprocs=2, join=True)
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(2))
