@@ -600,6 +600,44 @@ extern "C" int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t s
   return 0;
 }
 
+// Single-GPU stand-in for allreduce_twoshot256_kernel<2, true>: same instruction mix and bytes per element (two gradient
+// reads, one parameter read, two parameter writes), all on local memory and without flags.  bench/interference.py runs
+// it beside a GEMM to separate SM/L2/HBM interference from NVLink effects.
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
+stream_probe_kernel(const uint8_t* a, const uint8_t* b, uint8_t* p, uint8_t* q, long long nvec32, float lr) {
+  const long long stride = static_cast<long long>(gridDim.x) * THREADS;
+  for (long long v0 = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v0 < nvec32; v0 += stride * 2) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= nvec32) break;
+      const size_t off = static_cast<size_t>(v) * 32;
+      const V8 ra = ld256_stream(a + off), rb = ld256_stream(b + off), rp = ld256_stream(p + off);
+      V8 out;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ra.w[j]));
+        const float2 fb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rb.w[j]));
+        const float2 fp = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rp.w[j]));
+        __nv_bfloat162 h = __floats2bfloat162_rn(fp.x - lr * 0.5f * (fa.x + fb.x), fp.y - lr * 0.5f * (fa.y + fb.y));
+        out.w[j] = *reinterpret_cast<uint32_t*>(&h);
+      }
+      st256_stream(p + off, out);
+      st256_stream(q + off, out);
+    }
+  }
+}
+
+extern "C" int dtb_debug_stream_probe(const void* a, const void* b, void* p, void* q, long long bytes, int ctas,
+                                      void* stream) {
+  DTB_REQUIRE(bytes % 32 == 0 && ctas > 0 && ctas <= 1024, "dtb_debug_stream_probe: bytes must be a multiple of 32");
+  stream_probe_kernel<<<ctas, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(a), static_cast<const uint8_t*>(b), static_cast<uint8_t*>(p), static_cast<uint8_t*>(q),
+      bytes / 32, 0.f);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
 extern "C" int dtb_comm_error_flag(const dtb_comm* c) {
   if (c == nullptr) return -1;
   uint32_t v = 0;

@@ -87,6 +87,30 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// wait with cluster-scope acquire: pairs with a remote arrive.release.cluster so that data another CTA of the cluster
+// stored into this CTA's shared memory before arriving is visible afterwards
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+
+// store a word at the same shared-memory offset of another CTA in the cluster
+__device__ __forceinline__ void st_shared_cluster_u32(void* local_ptr, uint32_t cta_rank, uint32_t value) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(cta_rank));
+  asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(remote), "r"(value) : "memory");
+}
+
 // ----------------------------------------------------------------------------
 // TMA (bulk tensor copies).  Coordinates are innermost-first.
 // ----------------------------------------------------------------------------

@@ -15,6 +15,10 @@
 #include <cuda.h>
 #include <cstdlib>
 #include <cuda_bf16.h>
+
+#include <map>
+#include <mutex>
+#include <utility>
 #include <cuda_runtime.h>
 
 #include "../../include/dtb200.h"
@@ -60,7 +64,13 @@ struct Params {
   // raw fp32 accumulators to ws[s][M][N]; splitk_reduce_kernel adds the slices in order and runs the epilogue.
   int split_k, kb_per_split;
   float* ws;
+  // ---- dynamic tile scheduling: after its first (static) tile a cluster takes work units from this global counter,
+  // so an SM slowed down by a co-resident communication CTA simply ends up doing fewer tiles.  nullptr = static
+  // round-robin.  The fetch that hands out the last unit resets the counter, so it is zero again at kernel exit.
+  int* sched;
 };
+
+constexpr int SCHED_DEPTH = 4;       // ring of published tile ids per CTA
 
 constexpr int GATHER_ROWS = 16;      // rows per gather piece
 
@@ -380,6 +390,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   uint64_t* tmem_full = bars + 2 * STAGES;    // [2]
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;  // [2]
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* sched_full = bars + 2 * STAGES + 5;    // [SCHED_DEPTH] per CTA: tile id published
+  uint64_t* sched_empty = bars + 2 * STAGES + 9;   // [SCHED_DEPTH] leader only: every consumer of the cluster has read it
+  int* sched_tile = reinterpret_cast<int*>(bars + 2 * STAGES + 13);   // [SCHED_DEPTH]
+  static_assert((2 * STAGES + 13) * 8 + SCHED_DEPTH * 4 <= 256, "barrier block is 256 bytes");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -401,6 +415,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       mbar_init(&tmem_full[a], 1);
       mbar_init(&tmem_empty[a], NUM_EPI_WARPS * CG);
     }
+    for (int q = 0; q < SCHED_DEPTH; ++q) {
+      mbar_init(&sched_full[q], 1);
+      // consumers: leader CTA = MMA warp + epilogue warps, second CTA = TMA warp + epilogue warps
+      mbar_init(&sched_empty[q], (1 + NUM_EPI_WARPS) * CG);
+    }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -415,6 +434,26 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
+  // Consumer side of the tile ring (dynamic scheduling): the j-th published tile id of this cluster.  Called by whole
+  // warps; one lane tells the leader CTA that this warp is done with the slot.
+  const bool dyn = !GATHER && p.sched != nullptr;
+  auto next_tile = [&](int tile, int& j) -> int {
+    if (!dyn) return tile + num_clusters;
+    const int slot = j & (SCHED_DEPTH - 1);
+    mbar_wait_cluster(&sched_full[slot], (j / SCHED_DEPTH) & 1);
+    const int t = *reinterpret_cast<volatile int*>(&sched_tile[slot]);
+    __syncwarp();
+    if (lane == 0) {
+      if (CG == 1 || leader) {
+        mbar_arrive(&sched_empty[slot]);
+      } else {
+        mbar_arrive_cluster(&sched_empty[slot], 0);
+      }
+    }
+    ++j;
+    return t;
+  };
+
   if (warp == 0) {
     // ============================ TMA producer ============================
     // The whole warp walks the loop so every address / coordinate stays in uniform registers;
@@ -422,7 +461,35 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     // in a vote / R2UR waterfall).
     int stage = 0;
     uint32_t phase = 0;
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+    // Dynamic scheduling: this warp of the leader CTA is the scheduler.  At the start of a tile it takes the NEXT work
+    // unit from the global counter (the atomic's latency hides behind the first loads) and publishes it to both CTAs
+    // one k-block later, so nobody ever waits for a tile id and a cluster is committed only one tile ahead.
+    const bool scheduler = dyn && (CG == 1 || leader);
+    int fetched = 0, published = 0, consumed = 0;
+    auto publish = [&]() -> int {
+      const int nxt = __shfl_sync(0xffffffffu, fetched, 0);
+      const int slot = published & (SCHED_DEPTH - 1);
+      mbar_wait_cluster(&sched_empty[slot], ((published / SCHED_DEPTH) & 1) ^ 1);
+      if (lane == 0) {
+        if (nxt - num_clusters == num_tiles - 1) atomicExch(p.sched, 0);   // that was the last fetch of this launch
+        *reinterpret_cast<volatile int*>(&sched_tile[slot]) = nxt;
+        mbar_arrive(&sched_full[slot]);
+        if constexpr (CG == 2) {
+          st_shared_cluster_u32(&sched_tile[slot], 1, static_cast<uint32_t>(nxt));
+          mbar_arrive_cluster(&sched_full[slot], 1);
+        }
+      }
+      __syncwarp();
+      ++published;
+      return nxt;
+    };
+    for (int tile = cluster_id; tile < num_tiles;) {
+      bool pending = false;
+      int following = 0;
+      if (scheduler) {
+        if (lane == 0) fetched = num_clusters + atomicAdd(p.sched, 1);
+        pending = true;
+      }
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
       const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
@@ -482,7 +549,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           stage = 0;
           phase ^= 1;
         }
+        if (pending && kb >= kb_lo + 1) {
+          following = publish();
+          pending = false;
+        }
       }
+      if (pending) following = publish();
+      tile = scheduler ? following : next_tile(tile, consumed);
     }
   } else if (warp == 1) {
     // ============================= MMA issuer =============================
@@ -502,7 +575,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int consumed = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -588,7 +662,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     const int quad = warp & 3;   // TMEM lane quadrant this warp may access
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+    int consumed = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
       const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
@@ -795,6 +870,24 @@ static int dispatch_major(const CUtensorMap& ma, const CUtensorMap& mb, const Pa
 }  // namespace gemm
 }  // namespace dtb
 
+// One work counter per (device, stream) for dynamic tile scheduling.  Kernels on one stream run in order and every
+// launch leaves its counter at zero, so a stream can share one counter between all its GEMMs; GEMMs on different
+// streams may overlap and must not share.  First use on a stream allocates 256 bytes (not capturable: warm up first).
+static int* sched_counter(cudaStream_t s) {
+  static std::mutex mu;
+  static std::map<std::pair<int, cudaStream_t>, int*> table;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = table.find({dev, s});
+  if (it != table.end()) return it->second;
+  int* ptr = nullptr;
+  if (cudaMalloc(&ptr, 256) != cudaSuccess) return nullptr;
+  if (cudaMemset(ptr, 0, 256) != cudaSuccess) return nullptr;
+  table[{dev, s}] = ptr;
+  return ptr;
+}
+
 static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* stream) {
   using namespace dtb;
   using namespace dtb::gemm;
@@ -927,6 +1020,12 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
     grid = static_cast<int>(tiles < max_ctas ? tiles : max_ctas);
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  {
+    // dynamic scheduling whenever a cluster has more than one tile to do (DTB_GEMM_DYNAMIC=0: static round-robin)
+    static const int dynamic = [] { const char* e = getenv("DTB_GEMM_DYNAMIC"); return (e && e[0] == '0') ? 0 : 1; }();
+    const long long clusters = cg == 2 ? grid / 2 : grid;
+    if (dynamic && g == nullptr && tiles > clusters) p.sched = sched_counter(s);
+  }
   if (g != nullptr) {
     if (cg == 2) return launch<2, 256, 0, 0, true>(ma, mb, p, grid, s);
     if (bn == 256) return launch<1, 256, 0, 0, true>(ma, mb, p, grid, s);

@@ -478,5 +478,9 @@ def comm_rs_optim(desc: CommDesc, grad_offset: int, shard_offset: int, master, m
                                 _cta_arg(max_ctas, channel), _stream()))
 
 
+def debug_stream_probe(a, b, p, q, nbytes: int, ctas: int):
+    _ok(lib().dtb_debug_stream_probe(_p(a), _p(b), _p(p), _p(q), C.c_longlong(nbytes), ctas, _stream()))
+
+
 def comm_error_flag(desc: CommDesc) -> int:
     return int(lib().dtb_comm_error_flag(C.byref(desc)))

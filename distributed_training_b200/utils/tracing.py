@@ -26,3 +26,73 @@ def nvtx_range(name: str) -> Iterator[None]:
             torch.cuda.nvtx.range_pop()
     else:
         yield
+
+
+class KernelTimeline:
+    """Device-side timeline of the native launches of a few steps, without a profiler.
+
+    While active, selected wrappers of ``ops.native`` are bracketed by CUDA events on the stream they launch on;
+    ``rows()`` returns ``{"name", "detail", "stream", "start_ms", "ms"}`` relative to the first launch.  Events
+    cost ~2 µs of host time each and do not serialise streams, so overlap between the compute and comm streams is
+    visible as overlapping intervals.  Used by ``bench/step_timeline.py`` to see WHICH kernels stretch when the
+    gradient reduction runs beside them.
+    """
+
+    DEFAULT = ("gemm", "gemm_allgather", "colsum", "colsum_split", "cross_entropy_fwd_bwd", "mse_fwd_bwd",
+               "attention_fwd", "attention_bwd", "layernorm_fwd", "layernorm_bwd", "embedding_fwd", "embedding_bwd",
+               "multi_tensor_sgd", "multi_tensor_adamw", "comm_all_reduce_avg", "comm_all_reduce_sgd",
+               "comm_all_gather", "comm_reduce_scatter_avg", "comm_rs_optim", "comm_broadcast")
+
+    def __init__(self, names=DEFAULT) -> None:
+        self.names = tuple(names)
+        self._saved = {}
+        self._records = []
+
+    def __enter__(self) -> "KernelTimeline":
+        from ..ops import native
+
+        for n in self.names:
+            orig = getattr(native, n, None)
+            if orig is None:
+                continue
+            self._saved[n] = orig
+            setattr(native, n, self._wrap(n, orig))
+        return self
+
+    def __exit__(self, *exc) -> None:
+        from ..ops import native
+
+        for n, orig in self._saved.items():
+            setattr(native, n, orig)
+        self._saved.clear()
+
+    def _wrap(self, name, fn):
+        def traced(*args, **kwargs):
+            stream = torch.cuda.current_stream()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            out = fn(*args, **kwargs)
+            e1.record(stream)
+            detail = ""
+            if name.startswith("gemm"):
+                detail = f"{kwargs.get('m')}x{kwargs.get('n')}x{kwargs.get('k')}"
+            elif "numel" in kwargs:
+                detail = str(kwargs["numel"])
+            elif name.startswith("comm_all_reduce") and len(args) >= 3:
+                detail = str(args[3] if name.endswith("sgd") else args[2])
+            self._records.append((name, detail, stream.cuda_stream, e0, e1))
+            return out
+
+        return traced
+
+    def rows(self):
+        torch.cuda.synchronize()
+        if not self._records:
+            return []
+        t0 = self._records[0][3]
+        streams = {}
+        out = []
+        for name, detail, sid, e0, e1 in self._records:
+            out.append({"name": name, "detail": detail, "stream": streams.setdefault(sid, len(streams)),
+                        "start_ms": round(t0.elapsed_time(e0), 4), "ms": round(e0.elapsed_time(e1), 4)})
+        return out

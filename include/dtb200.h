@@ -230,6 +230,10 @@ int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t shard_offset
                       float weight_decay, float bias_corr1, float bias_corr2, float momentum, int max_ctas,
                       void* stream);
 /* error flag raised by a spin watchdog (0 = none); host-synchronous */
+/* Debug/benchmark only: single-GPU kernel with the memory traffic of a 2-rank fused all-reduce+SGD (3 reads, 2 writes
+ * per 32 bytes, no flags); p and q are updated in place from a, b.  Used by bench/interference.py. */
+int dtb_debug_stream_probe(const void* a, const void* b, void* p, void* q, long long bytes, int ctas, void* stream);
+
 int dtb_comm_error_flag(const dtb_comm* c);
 
 /* ---- host-side helpers for the symmetric heap --------------------------------- */
