@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--depth", type=int, default=DEPTH)
     ap.add_argument("--comm-ctas", type=int, default=0)
+    ap.add_argument("--comm-ce", type=int, default=-1, help="1/0: copy-engine path for large all-reduces")
+    ap.add_argument("--comm-exclusive", type=int, default=-1,
+                    help="whole-SM comm CTAs for large all-reduces (0 = co-resident mode, -1 = library default)")
     return ap.parse_args()
 
 
@@ -123,6 +126,10 @@ def run_ours(args):
     trainer = Trainer(model, [], OptimizerSpec("sgd", lr=args.lr), cfg, env, strategy=strategy)
     if args.comm_ctas and strategy.comm is not None:
         strategy.comm.comm_ctas = args.comm_ctas
+    if args.comm_ce >= 0 and strategy.comm is not None and hasattr(strategy.comm, "copy_engine"):
+        strategy.comm.copy_engine = bool(args.comm_ce)
+    if args.comm_exclusive >= 0 and strategy.comm is not None and hasattr(strategy.comm, "exclusive_sms"):
+        strategy.comm.exclusive_sms = args.comm_exclusive
     assert trainer.model.native_step, "the native tcgen05 path must be the one that runs"
 
     pool = pinned_pool(args.batch, args.width)

@@ -26,6 +26,8 @@ def main() -> None:
     ap.add_argument("--width", type=int, default=8192)
     ap.add_argument("--depth", type=int, default=8)
     ap.add_argument("--comm-ctas", type=int, default=0)
+    ap.add_argument("--comm-ce", type=int, default=-1, help="1/0: copy-engine path for large all-reduces")
+    ap.add_argument("--comm-exclusive", type=int, default=-1)
     ap.add_argument("--no-sync", action="store_true", help="skip the gradient reduction (compute-only step)")
     ap.add_argument("--out", default="gpurun_out/timeline.json")
     args = ap.parse_args()
@@ -42,7 +44,9 @@ def main() -> None:
     from distributed_training_b200.utils.timing import max_over_ranks, time_steps_ms
     from distributed_training_b200.utils.tracing import KernelTimeline
 
-    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    for key, val in (("MASTER_ADDR", "127.0.0.1"), ("MASTER_PORT", "29533"), ("RANK", "0"), ("LOCAL_RANK", "0"),
+                     ("WORLD_SIZE", "1")):
+        os.environ.setdefault(key, val)
     rank, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     native.require()
     env = DistributedEnvironment("cuda")
@@ -57,6 +61,10 @@ def main() -> None:
     trainer = Trainer(model, [], OptimizerSpec("sgd", lr=1e-4), cfg, env, strategy=strategy)
     if args.comm_ctas and strategy.comm is not None:
         strategy.comm.comm_ctas = args.comm_ctas
+    if args.comm_ce >= 0 and strategy.comm is not None and hasattr(strategy.comm, "copy_engine"):
+        strategy.comm.copy_engine = bool(args.comm_ce)
+    if args.comm_exclusive >= 0 and strategy.comm is not None and hasattr(strategy.comm, "exclusive_sms"):
+        strategy.comm.exclusive_sms = args.comm_exclusive
     x = torch.randn(args.batch, args.width, device=device).to(torch.bfloat16)
     y = torch.randint(0, args.width, (args.batch,), device=device)
 

@@ -235,8 +235,14 @@ __device__ __forceinline__ void st256_stream(void* p, const V8& v) {
 
 // bf16 two-shot mean (optionally fused with SGD) on 32-byte vectors; same semantics and reduction order as
 // allreduce_twoshot_kernel.  Peers are read four at a time to stay within the 64-register budget.
-template <int W, bool SGD>
-__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
+//
+// NT = 256: co-resident mode (fits next to a GEMM CTA).  NT = 1024: exclusive mode -- a CTA takes a whole SM (1024
+// threads x 64 registers = the entire register file), is launched in clusters of two so a pair fills one TPC, and a
+// handful of them (16 by default) carry the whole reduction.  The GEMM's dynamic tile scheduler routes work around the
+// SMs they occupy; measured on B200 that costs the GEMM ~11 % while the reduction runs instead of 20-35 % for
+// co-resident CTAs that fight the GEMM's TMA traffic for the SM's L1/shared-memory datapath (profiles/README.md).
+template <int W, bool SGD, int NT>
+__global__ void __launch_bounds__(NT, NT == THREADS ? MIN_CTAS_PER_SM : 1)
 allreduce_twoshot256_kernel(const Ctx x, size_t offset, long long nvec32, const SgdArgs sgd) {
   constexpr int G = W < 4 ? W : 4;          // loads in flight per batch
   constexpr int U = W <= 2 ? 2 : 1;
@@ -244,8 +250,8 @@ allreduce_twoshot256_kernel(const Ctx x, size_t offset, long long nvec32, const 
   rank_barrier(x, seq);
   const long long lo = nvec32 * x.c.rank / W, hi = nvec32 * (x.c.rank + 1) / W;
   const float scale = 1.f / W;
-  const long long stride = static_cast<long long>(gridDim.x) * THREADS;
-  for (long long v0 = lo + static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v0 < hi; v0 += stride * U) {
+  const long long stride = static_cast<long long>(gridDim.x) * NT;
+  for (long long v0 = lo + static_cast<long long>(blockIdx.x) * NT + threadIdx.x; v0 < hi; v0 += stride * U) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long v = v0 + u * stride;
@@ -468,6 +474,29 @@ using namespace dtb::comm;
 // The channel rides in the upper bits of max_ctas (bits 16..19) so the public signatures stay small.
 static inline int channel_of(int max_ctas) { return (max_ctas >> 16) & 0xF; }
 static inline int ctas_of(int max_ctas) { return max_ctas & 0xFFFF; }
+static inline bool exclusive_of(int max_ctas) { return ((max_ctas >> 20) & 1) != 0; }
+constexpr int EXCLUSIVE_THREADS = 1024;
+
+// Exclusive-mode launch of the 256-bit two-shot kernel: `ctas` whole-SM CTAs in clusters of two.
+template <int W, bool SGD>
+static cudaError_t launch_exclusive(const Ctx& x, size_t offset, long long nvec32, const SgdArgs& sgd, int ctas,
+                                    cudaStream_t s) {
+  if (ctas < 2) ctas = 2;
+  if (ctas > MAX_BLOCKS) ctas = MAX_BLOCKS;
+  ctas &= ~1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(ctas));
+  cfg.blockDim = dim3(EXCLUSIVE_THREADS);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, allreduce_twoshot256_kernel<W, SGD, EXCLUSIVE_THREADS>, x, offset, nvec32, sgd);
+}
 
 extern "C" int dtb_comm_barrier(const dtb_comm* c, int channel, void* stream) {
   if (check(c, channel)) return 2;
@@ -518,7 +547,8 @@ extern "C" int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long lo
     const bool wide = dtype == 0 && offset % 32 == 0 && (n * esize) % 32 == 0 && wide_enabled();
     DISPATCH_W(c->world, {
       if (dtype == 1) allreduce_twoshot_kernel<true, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
-      else if (wide) allreduce_twoshot256_kernel<W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec / 2, none);
+      else if (wide && exclusive_of(max_ctas)) DTB_CUDA_OK((launch_exclusive<W, false>(x, offset, nvec / 2, none, ctas_of(max_ctas), s)));
+      else if (wide) allreduce_twoshot256_kernel<W, false, THREADS><<<grid, THREADS, 0, s>>>(x, offset, nvec / 2, none);
       else allreduce_twoshot_kernel<false, W, false><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
     });
   }
@@ -539,7 +569,8 @@ extern "C" int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, si
   auto s = static_cast<cudaStream_t>(stream);
   const bool wide = grad_offset % 32 == 0 && param_offset % 32 == 0 && (n * 2) % 32 == 0 && wide_enabled();
   DISPATCH_W(c->world, {
-    if (wide) allreduce_twoshot256_kernel<W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec / 2, sgd);
+    if (wide && exclusive_of(max_ctas)) DTB_CUDA_OK((launch_exclusive<W, true>(x, grad_offset, nvec / 2, sgd, ctas_of(max_ctas), s)));
+    else if (wide) allreduce_twoshot256_kernel<W, true, THREADS><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec / 2, sgd);
     else allreduce_twoshot_kernel<false, W, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, sgd);
   });
   DTB_LAUNCH_OK();
@@ -600,6 +631,64 @@ extern "C" int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t s
   return 0;
 }
 
+// ---- copy-engine two-shot ----------------------------------------------------------------------------------------
+// The NVLink legs of a large all-reduce are plain copies; issued from SM threads they share an SM's L1/shared-memory
+// datapath with the resident GEMM CTA's TMA traffic and cost the GEMM 20-35 % (bench/interference.py), while the same
+// bytes moved by the copy engines cost it < 8 %.  So for big buckets: barrier kernel -> DMA the W-1 peer copies of my
+// slice into a local staging buffer -> ONE local kernel (sum in rank order, 1/W, cast, optional SGD) -> DMA the result
+// slice to every peer -> barrier kernel.  Only the short local kernel competes with the GEMM for SM resources.
+struct SliceArgs {
+  const uint8_t* own;       // my own copy of the slice (gradients)
+  const uint8_t* staged;    // W-1 peer copies, in rank order with my rank skipped
+  uint8_t* dst;             // mean gradient (in place) or, with sgd, the parameter slice
+  int rank;
+  int sgd;
+  float lr, decay;
+};
+
+template <int W>
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
+slice_reduce_kernel(const SliceArgs a, long long nvec32, long long slice_bytes) {
+  const float scale = 1.f / W;
+  const long long stride = static_cast<long long>(gridDim.x) * THREADS;
+  for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec32; v += stride) {
+    const size_t off = static_cast<size_t>(v) * 32;
+    float acc[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < W; ++r) {       // fixed rank order: identical rounding no matter which rank owns the slice
+      const uint8_t* src = (r == a.rank) ? a.own + off : a.staged + static_cast<size_t>(r < a.rank ? r : r - 1) * slice_bytes + off;
+      const V8 raw = ld256_stream(src);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.w[j]));
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+    if (a.sgd) {
+      const V8 praw = ld256_stream(a.dst + off);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&praw.w[j]));
+        acc[2 * j] = f.x * a.decay - a.lr * (acc[2 * j] * scale);
+        acc[2 * j + 1] = f.y * a.decay - a.lr * (acc[2 * j + 1] * scale);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) acc[j] *= scale;
+    }
+    V8 out;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+      out.w[j] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    st256_stream(a.dst + off, out);
+  }
+}
+
 // Single-GPU stand-in for allreduce_twoshot256_kernel<2, true>: same instruction mix and bytes per element (two gradient
 // reads, one parameter read, two parameter writes), all on local memory and without flags.  bench/interference.py runs
 // it beside a GEMM to separate SM/L2/HBM interference from NVLink effects.
@@ -626,6 +715,57 @@ stream_probe_kernel(const uint8_t* a, const uint8_t* b, uint8_t* p, uint8_t* q, 
       st256_stream(q + off, out);
     }
   }
+}
+
+extern "C" int dtb_comm_all_reduce_ce(const dtb_comm* c, size_t grad_offset, size_t param_offset, int sgd, long long n,
+                                      void* staging, size_t staging_bytes, float lr, float weight_decay, int max_ctas,
+                                      void* stream) {
+  if (check(c, channel_of(max_ctas))) return 2;
+  const int W = c->world;
+  const long long total = n * 2;
+  DTB_REQUIRE(W >= 2, "dtb_comm_all_reduce_ce: needs at least two ranks");
+  DTB_REQUIRE(n > 0 && total % (static_cast<long long>(W) * 32) == 0 && grad_offset % 32 == 0 && param_offset % 32 == 0,
+              "dtb_comm_all_reduce_ce: the buffer must split into 32-byte-granular slices per rank");
+  const long long slice = total / W;
+  DTB_REQUIRE(staging != nullptr && staging_bytes >= static_cast<size_t>(slice) * (W - 1) &&
+                  (reinterpret_cast<uintptr_t>(staging) & 31) == 0,
+              "dtb_comm_all_reduce_ce: staging must hold world-1 slices (%lld bytes)", slice * (W - 1));
+  Ctx x = {*c, channel_of(max_ctas)};
+  auto s = static_cast<cudaStream_t>(stream);
+  const int r = c->rank;
+  uint8_t* mine = static_cast<uint8_t*>(c->peers[r]);
+  // every rank's bucket is complete (each rank's comm stream waited for its own producer before this point)
+  barrier_kernel<<<1, THREADS, 0, s>>>(x);
+  DTB_LAUNCH_OK();
+  int j = 0;
+  for (int p = 0; p < W; ++p) {
+    if (p == r) continue;
+    DTB_CUDA_OK(cudaMemcpyAsync(static_cast<uint8_t*>(staging) + static_cast<size_t>(j) * slice,
+                                static_cast<const uint8_t*>(c->peers[p]) + grad_offset + static_cast<size_t>(r) * slice,
+                                static_cast<size_t>(slice), cudaMemcpyDefault, s));
+    ++j;
+  }
+  SliceArgs a = {};
+  a.own = mine + grad_offset + static_cast<size_t>(r) * slice;
+  a.staged = static_cast<const uint8_t*>(staging);
+  const size_t dst_off = (sgd ? param_offset : grad_offset) + static_cast<size_t>(r) * slice;
+  a.dst = mine + dst_off;
+  a.rank = r;
+  a.sgd = sgd;
+  a.lr = lr;
+  a.decay = 1.f - lr * weight_decay;
+  const int grid = pick_grid(slice / 32, ctas_of(max_ctas), 128);
+  DISPATCH_W(W, { slice_reduce_kernel<W><<<grid, THREADS, 0, s>>>(a, slice / 32, slice); });
+  DTB_LAUNCH_OK();
+  for (int p = 0; p < W; ++p) {
+    if (p == r) continue;
+    DTB_CUDA_OK(cudaMemcpyAsync(static_cast<uint8_t*>(c->peers[p]) + dst_off, mine + dst_off, static_cast<size_t>(slice),
+                                cudaMemcpyDefault, s));
+  }
+  // once every peer has passed this barrier, all their pushes into my buffer have completed
+  barrier_kernel<<<1, THREADS, 0, s>>>(x);
+  DTB_LAUNCH_OK();
+  return 0;
 }
 
 extern "C" int dtb_debug_stream_probe(const void* a, const void* b, void* p, void* q, long long bytes, int ctas,

@@ -64,9 +64,9 @@ struct Params {
   // raw fp32 accumulators to ws[s][M][N]; splitk_reduce_kernel adds the slices in order and runs the epilogue.
   int split_k, kb_per_split;
   float* ws;
-  // ---- dynamic tile scheduling: after its first (static) tile a cluster takes work units from this global counter,
-  // so an SM slowed down by a co-resident communication CTA simply ends up doing fewer tiles.  nullptr = static
-  // round-robin.  The fetch that hands out the last unit resets the counter, so it is zero again at kernel exit.
+  // ---- dynamic tile scheduling: clusters take work units from this global counter, so an SM slowed down by a
+  // co-resident communication CTA ends up doing fewer tiles and a cluster whose SMs are held by another kernel joins
+  // late (or not at all).  nullptr = static round-robin.  The last fetch of a launch resets the counter to zero.
   int* sched;
 };
 
@@ -471,7 +471,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       const int slot = published & (SCHED_DEPTH - 1);
       mbar_wait_cluster(&sched_empty[slot], ((published / SCHED_DEPTH) & 1) ^ 1);
       if (lane == 0) {
-        if (nxt - num_clusters == num_tiles - 1) atomicExch(p.sched, 0);   // that was the last fetch of this launch
+        // every cluster fetches until it is handed a unit past the end: num_tiles + num_clusters fetches per launch
+        if (nxt == num_tiles + num_clusters - 1) atomicExch(p.sched, 0);
         *reinterpret_cast<volatile int*>(&sched_tile[slot]) = nxt;
         mbar_arrive(&sched_full[slot]);
         if constexpr (CG == 2) {
@@ -483,11 +484,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       ++published;
       return nxt;
     };
-    for (int tile = cluster_id; tile < num_tiles;) {
+    int tile = cluster_id;
+    if (scheduler) {           // the first tile comes from the counter too: a cluster that starts late (its SMs were
+      if (lane == 0) fetched = atomicAdd(p.sched, 1);   // held by another kernel) finds only what is still undone
+      tile = publish();
+    } else if (dyn) {
+      tile = next_tile(0, consumed);
+    }
+    while (tile < num_tiles) {
       bool pending = false;
       int following = 0;
       if (scheduler) {
-        if (lane == 0) fetched = num_clusters + atomicAdd(p.sched, 1);
+        if (lane == 0) fetched = atomicAdd(p.sched, 1);
         pending = true;
       }
       int bi, m_blk, n_blk;
@@ -576,7 +584,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       int acc = 0;
       uint32_t acc_phase = 0;
       int consumed = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
+      for (int tile = dyn ? next_tile(0, consumed) : cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -663,7 +671,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     int acc = 0;
     uint32_t acc_phase = 0;
     int consumed = 0;
-    for (int tile = cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
+    for (int tile = dyn ? next_tile(0, consumed) : cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
       const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;

@@ -430,8 +430,11 @@ def symm_free(ptr: int) -> None:
     _ok(lib().dtb_symm_free(C.c_void_p(ptr)))
 
 
+EXCLUSIVE = 1 << 20     # OR into max_ctas: whole-SM (1024-thread) comm CTAs instead of co-resident 256-thread ones
+
+
 def _cta_arg(max_ctas: int, channel: int) -> int:
-    return (max_ctas & 0xFFFF) | ((channel & 0xF) << 16)
+    return (max_ctas & 0xFFFF) | ((channel & 0xF) << 16) | (max_ctas & EXCLUSIVE)
 
 
 def comm_barrier(desc: CommDesc, channel: int = 0):
@@ -454,6 +457,15 @@ def comm_all_reduce_sgd(desc: CommDesc, grad_offset: int, param_offset: int, num
     _ok(lib().dtb_comm_all_reduce_sgd(C.byref(desc), C.c_size_t(grad_offset), C.c_size_t(param_offset),
                                       C.c_longlong(numel), C.c_float(lr), C.c_float(weight_decay),
                                       _cta_arg(max_ctas, channel), _stream()))
+
+
+def comm_all_reduce_ce(desc: CommDesc, grad_offset: int, param_offset: int, sgd: bool, numel: int,
+                       staging: torch.Tensor, lr: float = 0.0, weight_decay: float = 0.0, max_ctas: int = 0,
+                       channel: int = 0):
+    _ok(lib().dtb_comm_all_reduce_ce(C.byref(desc), C.c_size_t(grad_offset), C.c_size_t(param_offset), int(sgd),
+                                     C.c_longlong(numel), _p(staging),
+                                     C.c_size_t(staging.numel() * staging.element_size()), C.c_float(lr),
+                                     C.c_float(weight_decay), _cta_arg(max_ctas, channel), _stream()))
 
 
 def comm_all_gather(desc: CommDesc, dst_offset: int, src_offset: int, numel: int, esize: int, max_ctas: int = 0,

@@ -91,6 +91,15 @@ class SymmComm(Communicator):
         # CTA budget of a collective (0 = library default of 64): with 2 ranks each rank moves half of every
         # buffer, so more CTAs are needed to keep enough bytes in flight
         self.comm_ctas = comm_ctas if comm_ctas else (128 if self.world_size == 2 else 0)
+        #: > 0: large bf16 all-reduces run on this many whole-SM CTAs (clusters of two) instead of co-resident ones;
+        #: the GEMM's dynamic tile scheduler works around the SMs they hold.  DTB_COMM_EXCLUSIVE_SMS overrides.
+        self.exclusive_sms = int(os.environ.get("DTB_COMM_EXCLUSIVE_SMS", "0"))
+        self.exclusive_min_bytes = 8 << 20
+        #: large bf16 all-reduces move their NVLink legs with the copy engines (dtb_comm_all_reduce_ce) instead of SM
+        #: threads: a GEMM running beside them loses < 8 % to DMA traffic vs 20-35 % to co-resident load/store CTAs
+        self.copy_engine = os.environ.get("DTB_COMM_CE", "1") != "0"
+        self.copy_engine_min_bytes = 16 << 20
+        self._ce_staging: List[torch.Tensor] = []
         self.segments: List[Segment] = []
         self._owner_of: Dict[int, Tuple[Segment, int]] = {}   # storage data_ptr -> (segment, offset)
         self.stream = torch.cuda.Stream(self.device, priority=-1) if overlap_stream else None
@@ -214,14 +223,35 @@ class SymmComm(Communicator):
         flush()
         torch.cuda.current_stream().synchronize()
 
+    def _ctas_for(self, nbytes: int) -> int:
+        if self.exclusive_sms > 0 and nbytes >= self.exclusive_min_bytes:
+            return self.exclusive_sms | native.EXCLUSIVE
+        return self.comm_ctas
+
+    def _ce_scratch(self, nbytes: int) -> Optional[torch.Tensor]:
+        """Local staging for the copy-engine path, or None when this buffer should take the SM path."""
+        w = self.world_size
+        if not self.copy_engine or w < 2 or nbytes < self.copy_engine_min_bytes or nbytes % (w * 32):
+            return None
+        need = nbytes // w * (w - 1)
+        if not self._ce_staging or self._ce_staging[-1].numel() < need:
+            # never freed or shrunk while the communicator lives: kernels on the comm stream may still read it
+            self._ce_staging.append(torch.empty(need, dtype=torch.uint8, device=self.device))
+        return self._ce_staging[-1]
+
     def all_reduce_avg_(self, buf: torch.Tensor) -> Work:
         if buf.dtype not in (torch.bfloat16, torch.float32):
             raise TypeError(f"all_reduce_avg_ supports bf16/fp32, got {buf.dtype}")
         seg, off = self.locate(buf)
         esize = buf.element_size()
         numel = (buf.numel() * esize + 15) // 16 * 16 // esize      # heap slots are padded to 256 B
+        staging = self._ce_scratch(numel * esize) if buf.dtype == torch.bfloat16 else None
         with self._on_comm_stream():
-            native.comm_all_reduce_avg(seg.desc, off, numel, buf.dtype == torch.float32, 0, self.comm_ctas)
+            if staging is not None:
+                native.comm_all_reduce_ce(seg.desc, off, off, False, numel, staging, max_ctas=self.comm_ctas)
+            else:
+                native.comm_all_reduce_avg(seg.desc, off, numel, buf.dtype == torch.float32, 0,
+                                           self._ctas_for(numel * esize))
             event = torch.cuda.Event()
             event.record()
         return _StreamWork(event)
@@ -236,8 +266,14 @@ class SymmComm(Communicator):
         if seg is not seg_p:
             raise ValueError("all_reduce_sgd_: grads and params must live in the same symmetric segment")
         numel = (grads.numel() * 2 + 15) // 16 * 8
+        staging = self._ce_scratch(numel * 2)
         with self._on_comm_stream():
-            native.comm_all_reduce_sgd(seg.desc, g_off, p_off, numel, lr, weight_decay, self.comm_ctas)
+            if staging is not None:
+                native.comm_all_reduce_ce(seg.desc, g_off, p_off, True, numel, staging, lr, weight_decay,
+                                          max_ctas=self.comm_ctas)
+            else:
+                native.comm_all_reduce_sgd(seg.desc, g_off, p_off, numel, lr, weight_decay,
+                                           self._ctas_for(numel * 2))
             event = torch.cuda.Event()
             event.record()
         return _StreamWork(event)

@@ -217,6 +217,14 @@ int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long long n, int d
  * and stores the NEW PARAMETERS into every rank.  The gradient buffers are left untouched. */
 int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, size_t param_offset, long long n, float lr,
                             float weight_decay, int max_ctas, void* stream);
+/* Large-bucket variant of the two calls above that moves the NVLink legs with the copy engines instead of SM
+ * threads (a resident GEMM loses < 8 % to DMA traffic but 20-35 % to co-resident load/store CTAs): barrier kernel,
+ * W-1 peer->staging copies of this rank's slice, one local reduce(+SGD when sgd != 0, else the mean gradient is
+ * written in place) kernel, W-1 slice pushes, barrier kernel -- all enqueued on `stream` by this one call.
+ * n*2 bytes must split into 32-byte-granular slices per rank; staging: local scratch of (world-1) * n*2/world bytes. */
+int dtb_comm_all_reduce_ce(const dtb_comm* c, size_t grad_offset, size_t param_offset, int sgd, long long n,
+                           void* staging, size_t staging_bytes, float lr, float weight_decay, int max_ctas,
+                           void* stream);
 /* dst[r*n .. (r+1)*n) = rank r's src[0..n)  (element size esize) */
 int dtb_comm_all_gather(const dtb_comm* c, size_t dst_offset, size_t src_offset, long long n, int esize,
                         int max_ctas, void* stream);

@@ -48,6 +48,35 @@ def collectives(rank, world, port, out_dir):
                     assert torch.equal(buf.cpu(), expect), (dtype, n, rep, (buf.cpu().float() - expect.float()).abs().max())
                     got = _gather_cpu(buf, world)
                     assert all(torch.equal(got[0], t) for t in got), "ranks disagree bitwise"
+        # ---- copy-engine path (what large buckets take): same contract; threshold lowered so small buffers use it ----
+        comm.copy_engine, comm.copy_engine_min_bytes = True, 1 << 16
+        for n in (world * 16 * 4096, world * 16 * 100_000):
+            comm.reserve(2 * n * 2 + 4096)
+            buf, par = comm.alloc(n, torch.bfloat16), comm.alloc(n, torch.bfloat16)
+            assert comm._ce_scratch(n * 2) is not None
+            for rep in range(3):
+                g = torch.Generator().manual_seed(77 * rep + n)
+                per_rank = [torch.randn(n, generator=g).to(torch.bfloat16) for _ in range(world)]
+                p0 = torch.randn(n, generator=g).to(torch.bfloat16)
+                acc = torch.zeros(n)
+                for r in range(world):
+                    acc += per_rank[r].float()
+                mean = acc / world
+                buf.copy_(per_rank[rank])
+                comm.all_reduce_avg_(buf).wait()
+                torch.cuda.synchronize()
+                assert torch.equal(buf.cpu(), mean.to(torch.bfloat16)), ("ce mean", n, rep)
+                # fused SGD: gradients stay untouched, every rank ends with the same new parameters
+                buf.copy_(per_rank[rank])
+                par.copy_(p0)
+                comm.all_reduce_sgd_(buf, par, 0.05, 0.01).wait()
+                torch.cuda.synchronize()
+                expect = p0.float() * (1 - 0.05 * 0.01) - 0.05 * mean
+                assert torch.allclose(par.cpu().float(), expect, rtol=2 ** -7, atol=1e-6), ("ce sgd", n, rep)
+                assert torch.equal(buf.cpu(), per_rank[rank]), "gradients must be left untouched"
+                got = _gather_cpu(par, world)
+                assert all(torch.equal(got[0], t) for t in got), "ranks disagree bitwise after ce sgd"
+        comm.copy_engine_min_bytes = 16 << 20
         # ---- broadcast ----
         t1 = torch.full((1000, 33), float(rank + 1), device=dev)
         t2 = torch.full((7,), float(rank + 5), device=dev, dtype=torch.bfloat16)
