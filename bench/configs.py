@@ -32,6 +32,7 @@ def main():
                          "(default: flat fp32 logits, the layout the product model uses)")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--timeline", default="", help="ours: write a per-kernel device timeline of one step to this file")
     ns = ap.parse_args()
     c = dict(CONFIGS[ns.config])
     if ns.batch:
@@ -87,6 +88,39 @@ def main():
         total = time_steps_ms(step, ns.steps)
         extra = {"launches_per_step": native.launch_count() / ns.steps,
                  "exposed_comm_ms": wrapped.exposed_comm_ms() if hasattr(wrapped, "exposed_comm_ms") else None}
+        # host time to ISSUE a step (no sync inside): when it approaches the device time the step is launch-bound
+        import time
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(3):
+            step(i)
+        extra["host_issue_ms_per_step"] = (time.perf_counter() - t0) / 3 * 1e3
+        torch.cuda.synchronize()
+        if ns.timeline:
+            from collections import defaultdict
+            from distributed_training_b200.utils.tracing import KernelTimeline
+            with KernelTimeline() as tl:
+                for i in range(2):
+                    torch.cuda.synchronize()
+                    mark = len(tl._records)
+                    step(i)
+                rows = tl.rows()[mark:]
+            base = rows[0]["start_ms"]
+            by = defaultdict(lambda: [0, 0.0])
+            for r in rows:
+                r["start_ms"] = round(r["start_ms"] - base, 4)
+                key = f"{r['name']} {r['detail']} s{r['stream']}"
+                by[key][0] += 1
+                by[key][1] += r["ms"]
+            busy = {}
+            for r in rows:
+                busy[r["stream"]] = busy.get(r["stream"], 0.0) + r["ms"]
+            if rank == 0:
+                Path(ns.timeline).parent.mkdir(parents=True, exist_ok=True)
+                Path(ns.timeline).write_text(json.dumps({
+                    "span_ms": max(r["start_ms"] + r["ms"] for r in rows), "busy_ms_by_stream": busy,
+                    "by_kernel": {k: {"n": v[0], "ms_total": round(v[1], 3)} for k, v in
+                                  sorted(by.items(), key=lambda kv: -kv[1][1])}, "rows": rows}, indent=1))
         strategy.comm.close()
     else:
         dist.init_process_group("cpu:gloo,cuda:nccl")

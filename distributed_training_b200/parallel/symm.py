@@ -95,9 +95,10 @@ class SymmComm(Communicator):
         #: the GEMM's dynamic tile scheduler works around the SMs they hold.  DTB_COMM_EXCLUSIVE_SMS overrides.
         self.exclusive_sms = int(os.environ.get("DTB_COMM_EXCLUSIVE_SMS", "0"))
         self.exclusive_min_bytes = 8 << 20
-        #: large bf16 all-reduces move their NVLink legs with the copy engines (dtb_comm_all_reduce_ce) instead of SM
-        #: threads: a GEMM running beside them loses < 8 % to DMA traffic vs 20-35 % to co-resident load/store CTAs
-        self.copy_engine = os.environ.get("DTB_COMM_CE", "1") != "0"
+        #: opt-in (DTB_COMM_CE=1): large bf16 all-reduces move their NVLink legs with the copy engines
+        #: (dtb_comm_all_reduce_ce).  Local DMA traffic barely slows a GEMM, but measured at 2 GPUs the peer copies ran
+        #: at ~1/3 of their solo rate beside the GEMMs and the step was 0.4 ms slower than with co-resident comm CTAs
+        self.copy_engine = os.environ.get("DTB_COMM_CE", "0") == "1"
         self.copy_engine_min_bytes = 16 << 20
         self._ce_staging: List[torch.Tensor] = []
         self.segments: List[Segment] = []
