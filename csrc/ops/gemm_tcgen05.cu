@@ -72,7 +72,8 @@ struct Params {
 
 constexpr int SCHED_DEPTH = 4;       // ring of published tile ids per CTA
 
-constexpr int GATHER_ROWS = 16;      // rows per gather piece
+constexpr int GATHER_ROWS = 16;         // rows per gather piece
+constexpr int GATHER_CHUNK_VECS = 128;  // 16-byte vectors (2 KB) of a row per gather piece
 
 template <int CG, int BN>
 struct Config {
@@ -267,31 +268,55 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&raw)[
   }
 }
 
-// Epilogue for a 64-column group of one warp's 32 rows, staged through shared memory so that every global
-// access is a full 128-byte row segment (a thread owns a TMEM lane = an output row, so un-staged stores touch
-// 32 different cache lines per instruction, which dominates GEMMs with a short K such as the GPT-2 layers).
-// `st_out` / `st_in`: this warp's two [32 x 128 B] buffers; 16-byte chunk j of row r lives at chunk j ^ (r & 7).
-// Requirements (checked by the caller): bf16 D / aux, N % 8 == 0.
-// Coalesced load of this warp's [32 rows x 64 cols] bf16 aux tile into registers (8 x 16 B per lane).
-__device__ __forceinline__ void load_aux_group(const Params& p, uint4 (&areg)[8], int row_base, int colg,
-                                               long long aux_off, int lane) {
-  const int sub = lane >> 3, seg = lane & 7;
-  const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + aux_off;
+// ---- staged epilogue ------------------------------------------------------------------------------------------
+// One warp owns 32 accumulator rows (a thread owns a TMEM lane = an output row), so un-staged stores touch 32
+// different cache lines per instruction.  Each 64-column group therefore goes TMEM -> registers -> this warp's
+// [32 x 128 B] shared-memory buffer (16-byte chunk j of row r lives at chunk j ^ (r & 7)) -> global memory with every
+// access a full 128-byte row segment.  Requirements (checked by the caller): bf16 D / aux, N % 8 == 0.
+//
+// The first version spent 221 SASS instructions per tcgen05.ld (ncu: the epilogue warps were issue-bound and a
+// GEMM with K = 768 took 6.5 us per tile for a 4.4 us main loop): 64-bit address arithmetic and bounds checks per
+// store, parameters re-read from the constant bank.  Everything that does not depend on the column group is now
+// computed once per tile (EpiTile), interior tiles skip all bounds checks, and the bias is fetched once per tile
+// into registers BEFORE the accumulator wait and handed out with warp shuffles.
+struct EpiTile {
+  uint8_t* out;          // &D[row_base + lane/8][n0 + (lane%8)*8]: this lane's first 16-byte segment
+  uint8_t* out2;         // same position in D2 (pre-activation copy) or nullptr
+  const uint8_t* aux;    // same position in aux or nullptr
+  long long step_d;      // bytes between rows r and r + 4 of D / D2
+  long long step_aux;
+  int row_base, n0;
+  bool interior;         // all 32 rows and all BN columns are in range
+  bool bias_regs;        // bias for the whole tile is held across the warp in `bias` (lane l: columns 8l .. 8l+7)
+  uint4 bias;
+};
+
+// Coalesced load of this warp's [32 rows x 64 cols] bf16 aux tile of column group `c2` (8 x 16 B per lane).
+__device__ __forceinline__ void load_aux_group(const Params& p, const EpiTile& t, uint4 (&areg)[8], int c2, int lane) {
+  const uint8_t* ap = t.aux + c2 * 128;
+  if (t.interior) {
 #pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int gr = row_base + it * 4 + sub, gc = colg + seg * 8;
-    areg[it] = make_uint4(0, 0, 0, 0);
-    if (gr < p.M && gc < p.N) areg[it] = *reinterpret_cast<const uint4*>(ap + static_cast<long long>(gr) * p.ld_aux + gc);
+    for (int it = 0; it < 8; ++it) areg[it] = __ldg(reinterpret_cast<const uint4*>(ap + it * t.step_aux));
+  } else {
+    const int sub = lane >> 3, gc = t.n0 + c2 * 64 + (lane & 7) * 8;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      areg[it] = make_uint4(0, 0, 0, 0);
+      if (t.row_base + it * 4 + sub < p.M && gc < p.N) areg[it] = __ldg(reinterpret_cast<const uint4*>(ap + it * t.step_aux));
+    }
   }
 }
 
-// `areg` holds this group's aux tile (loaded one group ahead so its HBM latency hides behind the previous
-// group's math); on return it holds the tile of `next_colg` (if >= 0).
-__device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t taddr, int row_base, int colg,
-                                                      long long d_off, long long aux_off, uint8_t* st_out,
-                                                      uint8_t* st_in, int lane, uint4 (&areg)[8], int next_colg) {
-  const int sub = lane >> 3, seg = lane & 7;          // coalesced phase: 4 rows x 8 segments of 16 B per step
-  const bool has_aux = (p.aux != nullptr) && (p.act != 1);
+// TMEM -> registers -> epilogue math -> shared memory for column group c2.  `areg` holds this group's aux tile
+// (loaded one group ahead so its latency hides behind the previous group's math); on return it holds the next one.
+__device__ __forceinline__ void epilogue_group_compute(const Params& p, const EpiTile& t, uint32_t taddr, int c2,
+                                                       int num_groups, uint8_t* st_out, uint8_t* st_in, int lane,
+                                                       uint4 (&areg)[8]) {
+  const int sub = lane >> 3, seg = lane & 7;
+  const bool has_aux = (t.aux != nullptr) && (p.act != 1);
+  const uint32_t xs = static_cast<uint32_t>(lane & 7) << 4;       // this row's chunk swizzle
+  uint8_t* my_out = st_out + lane * 128;
+  uint8_t* my_in = st_in + lane * 128;
   if (has_aux) {
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
@@ -299,20 +324,40 @@ __device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t 
       *reinterpret_cast<uint4*>(st_in + rl * 128 + ((seg ^ (rl & 7)) << 4)) = areg[it];
     }
     __syncwarp();
-    if (next_colg >= 0) load_aux_group(p, areg, row_base, next_colg, aux_off, lane);
+    if (c2 + 1 < num_groups) load_aux_group(p, t, areg, c2 + 1, lane);
   }
-  const bool want_z = (p.act == 1) && (p.d2 != nullptr);
+  const bool want_z = (p.act == 1) && (t.out2 != nullptr);
 #pragma unroll 1
   for (int half = 0; half < 2; ++half) {
-    const int col0 = colg + half * 32;
-    if (col0 >= p.N) break;
+    const int col0 = t.n0 + c2 * 64 + half * 32;
+    if (!t.interior && col0 >= p.N) break;
     uint32_t raw[32];
     tmem_ld_32x32b_x32(taddr + half * 32, raw);
     tmem_ld_wait();
     float v[32];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) * p.alpha;
-    if (p.bias != nullptr) add_bias32(p, v, col0);
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+    if (p.alpha != 1.0f) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+    }
+    if (t.bias_regs) {
+      const int src0 = (c2 * 2 + half) * 4;     // lanes holding these 32 columns
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t w0 = __shfl_sync(0xffffffffu, t.bias.x, src0 + q), w1 = __shfl_sync(0xffffffffu, t.bias.y, src0 + q);
+        const uint32_t w2 = __shfl_sync(0xffffffffu, t.bias.z, src0 + q), w3 = __shfl_sync(0xffffffffu, t.bias.w, src0 + q);
+        const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w0));
+        const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w1));
+        const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w2));
+        const float2 f3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w3));
+        v[8 * q + 0] += f0.x; v[8 * q + 1] += f0.y; v[8 * q + 2] += f1.x; v[8 * q + 3] += f1.y;
+        v[8 * q + 4] += f2.x; v[8 * q + 5] += f2.y; v[8 * q + 6] += f3.x; v[8 * q + 7] += f3.y;
+      }
+    } else if (p.bias != nullptr) {
+      add_bias32(p, v, col0);
+    }
+    const uint32_t hx = xs ^ static_cast<uint32_t>(half * 64);
     if (p.act == 1) {
       if (want_z) {
 #pragma unroll
@@ -322,7 +367,7 @@ __device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t 
           o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
           o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
           o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
-          *reinterpret_cast<uint4*>(st_in + lane * 128 + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+          *reinterpret_cast<uint4*>(my_in + (hx ^ (q * 16))) = o;
         }
       }
 #pragma unroll
@@ -330,8 +375,8 @@ __device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t 
     } else if (has_aux) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const uint4 t = *reinterpret_cast<const uint4*>(st_in + lane * 128 + (((half * 4 + q) ^ (lane & 7)) << 4));
-        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+        const uint4 a4 = *reinterpret_cast<const uint4*>(my_in + (hx ^ (q * 16)));
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&a4);
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const float2 f = __bfloat1622float2(h[e]);
@@ -352,20 +397,37 @@ __device__ __forceinline__ void epilogue_group_staged(const Params& p, uint32_t 
       o.y = pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
       o.z = pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
       o.w = pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
-      *reinterpret_cast<uint4*>(st_out + lane * 128 + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+      *reinterpret_cast<uint4*>(my_out + (hx ^ (q * 16))) = o;
     }
   }
   __syncwarp();
-  __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + d_off;
-  __nv_bfloat16* zp = reinterpret_cast<__nv_bfloat16*>(p.d2) + d_off;
+}
+
+// shared memory -> global memory for column group c2: 8 steps of 4 rows x 128 bytes per warp
+__device__ __forceinline__ void epilogue_group_store(const Params& p, const EpiTile& t, int c2, const uint8_t* st_out,
+                                                     const uint8_t* st_in, int lane) {
+  const int sub = lane >> 3, seg = lane & 7;
+  const bool want_z = (p.act == 1) && (t.out2 != nullptr);
+  // row rl = 4*it + sub sits at rl*128 + ((seg ^ (rl & 7)) << 4); (rl & 7) = sub for even it, sub + 4 for odd it
+  const uint32_t even = static_cast<uint32_t>(sub * 128 + ((seg ^ sub) << 4)), odd = even ^ 64u;
+  uint8_t* dp = t.out + c2 * 128;
+  uint8_t* zp = t.out2 + c2 * 128;
+  if (t.interior) {
 #pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int rl = it * 4 + sub, gr = row_base + rl, gc = colg + seg * 8;
-    if (gr < p.M && gc < p.N) {
-      const int so = rl * 128 + ((seg ^ (rl & 7)) << 4);
-      *reinterpret_cast<uint4*>(dp + static_cast<long long>(gr) * p.ldd + gc) = *reinterpret_cast<const uint4*>(st_out + so);
-      if (want_z)
-        *reinterpret_cast<uint4*>(zp + static_cast<long long>(gr) * p.ldd + gc) = *reinterpret_cast<const uint4*>(st_in + so);
+    for (int it = 0; it < 8; ++it) {
+      const uint32_t so = ((it & 1) ? odd : even) + it * 512;
+      *reinterpret_cast<uint4*>(dp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_out + so);
+      if (want_z) *reinterpret_cast<uint4*>(zp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_in + so);
+    }
+  } else {
+    const int gc = t.n0 + c2 * 64 + seg * 8;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const uint32_t so = ((it & 1) ? odd : even) + it * 512;
+      if (t.row_base + it * 4 + sub < p.M && gc < p.N) {
+        *reinterpret_cast<uint4*>(dp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_out + so);
+        if (want_z) *reinterpret_cast<uint4*>(zp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_in + so);
+      }
     }
   }
   __syncwarp();
@@ -506,7 +568,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       if constexpr (GATHER) {
         // every 16-row piece of this n-block has landed in the local matrix (written with generic stores by
         // gather warps of any CTA): acquire the counter, then order the async-proxy (TMA) reads after it
-        const int want = (min(BN, p.N - n_blk * BN) + GATHER_ROWS - 1) / GATHER_ROWS;
+        const int want = ((min(BN, p.N - n_blk * BN) + GATHER_ROWS - 1) / GATHER_ROWS) *
+                         ((p.K / 8 + GATHER_CHUNK_VECS - 1) / GATHER_CHUNK_VECS);
         while (ld_acquire_gpu(reinterpret_cast<const uint32_t*>(p.g_flags + n_blk)) < static_cast<uint32_t>(want)) {
         }
         asm volatile("fence.proxy.async.global;" ::: "memory");
@@ -628,35 +691,45 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   } else if (GATHER && warp >= NUM_THREADS / 32) {
     // ============================ gather warps ============================
     // Pieces are claimed from a global counter in the order the tiles will need them.
-    const int pieces_per_block = BN / GATHER_ROWS;
+    // A piece = 16 rows x up to 2 KB of one n-block (row groups x column chunks), so that even a matrix with few,
+    // long rows splits into enough pieces for every gather warp.  16 x 16 B per lane are in flight (8 KB per warp):
+    // a row-by-row copy of a K=1600 row is 6 dependent load->store round trips over NVLink, and then the gather, not
+    // the MMA, sets the kernel's time (measured 325 us for a 119 us GEMM before this loop was flattened).
+    const int row_vecs = static_cast<int>(p.K) / 8;                       // 16-byte vectors per row (K % 8 == 0)
+    const int col_chunks = (row_vecs + GATHER_CHUNK_VECS - 1) / GATHER_CHUNK_VECS;
+    const int pieces_per_block = (BN / GATHER_ROWS) * col_chunks;
     const int total_pieces = p.n_blocks * pieces_per_block;
     int* work = p.g_flags + p.n_blocks;
-    const long long row_bytes = static_cast<long long>(p.K) * 2;
+    const long long pitch = static_cast<long long>(p.g_ldb) * 2;
     while (true) {
       int piece = 0;
       if (lane == 0) piece = atomicAdd(work, 1);
       piece = __shfl_sync(0xffffffffu, piece, 0);
       if (piece >= total_pieces) break;
       const int n_blk = (piece / pieces_per_block + p.g_rotate) % p.n_blocks;
-      const int r0 = n_blk * BN + (piece % pieces_per_block) * GATHER_ROWS;
+      const int rem = piece % pieces_per_block;
+      const int r0 = n_blk * BN + (rem / col_chunks) * GATHER_ROWS;
+      const int c0 = (rem % col_chunks) * GATHER_CHUNK_VECS;
       if (r0 < p.N) {
         const int owner = r0 / p.g_rows_per_rank;
         const int nrows = min(GATHER_ROWS, p.N - r0);
+        const int width = min(GATHER_CHUNK_VECS, row_vecs - c0);
         const uint8_t* src = static_cast<const uint8_t*>(p.g_peer_shard[owner]) +
-                             static_cast<long long>(r0 - owner * p.g_rows_per_rank) * p.g_ldb * 2;
-        uint8_t* dst = static_cast<uint8_t*>(p.g_full) + static_cast<long long>(r0) * p.g_ldb * 2;
-        for (int r = 0; r < nrows; ++r) {
-          const uint8_t* srow = src + static_cast<long long>(r) * p.g_ldb * 2;
-          uint8_t* drow = dst + static_cast<long long>(r) * p.g_ldb * 2;
-          long long off = static_cast<long long>(lane) * 16;
-          for (; off + 7 * 512 < row_bytes; off += 8 * 512) {   // 8 x 16 B per lane in flight
-            uint4 v[8];
+                             static_cast<long long>(r0 - owner * p.g_rows_per_rank) * pitch + c0 * 16;
+        uint8_t* dst = static_cast<uint8_t*>(p.g_full) + static_cast<long long>(r0) * pitch + c0 * 16;
+#pragma unroll 1
+        for (int base = lane; base < GATHER_ROWS * GATHER_CHUNK_VECS; base += 16 * 32) {
+          uint4 v[16];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = ld_nc_v4(srow + off + u * 512);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) st_v4(drow + off + u * 512, v[u]);
+          for (int u = 0; u < 16; ++u) {
+            const int idx = base + u * 32, r = idx / GATHER_CHUNK_VECS, c = idx % GATHER_CHUNK_VECS;
+            if (r < nrows && c < width) v[u] = ld_nc_v4(src + r * pitch + c * 16);
           }
-          for (; off < row_bytes; off += 512) st_v4(drow + off, ld_nc_v4(srow + off));
+#pragma unroll
+          for (int u = 0; u < 16; ++u) {
+            const int idx = base + u * 32, r = idx / GATHER_CHUNK_VECS, c = idx % GATHER_CHUNK_VECS;
+            if (r < nrows && c < width) st_v4(dst + r * pitch + c * 16, v[u]);
+          }
         }
       }
       __syncwarp();
@@ -679,9 +752,51 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       const long long aux_off = b_in * p.aux_si + b_out * p.aux_so;
       const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BM + quad * 32 + lane;
       const int n0 = n_blk * BN;
+      // ---- per-tile setup, done BEFORE waiting for the accumulator so that the global loads issued here (bias, first
+      // aux group) are in flight while the MMAs of this tile still run
+      const bool staged = p.split_k == 1 && !p.direct_epilogue && !p.d_fp32 && !(p.aux != nullptr && p.aux_fp32) && (p.N & 7) == 0;
+      EpiTile et;
+      uint4 areg[8];
+      uint8_t* st_out = epi_stage + (warp - 2) * 8192;
+      const int num_groups = min(BN / 64, (p.N - n0 + 63) / 64);
+      if (staged) {
+        const int sub = lane >> 3, seg = lane & 7;
+        et.row_base = row - lane;
+        et.n0 = n0;
+        et.interior = (et.row_base + 32 <= p.M) && (n0 + BN <= p.N);
+        const long long elem0 = static_cast<long long>(et.row_base + sub) * p.ldd + n0 + seg * 8;
+        et.out = reinterpret_cast<uint8_t*>(p.d) + (d_off + elem0) * 2;
+        et.out2 = p.d2 != nullptr ? reinterpret_cast<uint8_t*>(p.d2) + (d_off + elem0) * 2 : nullptr;
+        et.step_d = p.ldd * 8;
+        et.aux = nullptr;
+        et.step_aux = p.ld_aux * 8;
+        if (p.aux != nullptr)
+          et.aux = reinterpret_cast<const uint8_t*>(p.aux) +
+                   (aux_off + static_cast<long long>(et.row_base + sub) * p.ld_aux + n0 + seg * 8) * 2;
+        et.bias_regs = false;
+        if (BN == 256 && p.bias != nullptr && !p.bias_fp32 && n0 + BN <= p.N &&
+            (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
+          et.bias_regs = true;       // 32 lanes x 8 columns = the tile's 256 columns
+          et.bias = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + n0) + lane);
+        }
+        if (et.aux != nullptr && p.act != 1) load_aux_group(p, et, areg, 0, lane);
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      // the accumulator stage is handed back to the MMA warp as soon as its last tcgen05.ld has completed -- before the
+      // final group's global stores, which would otherwise sit in front of the arrive's release fence
+      auto release_acc = [&]() {
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (CG == 1 || leader) {
+            mbar_arrive(&tmem_empty[acc]);
+          } else {
+            mbar_arrive_remote(&tmem_empty[acc], 0);
+          }
+        }
+      };
       if (p.split_k > 1) {
         // raw fp32 partial sums of this K-split: 128 contiguous bytes per thread and chunk
         float* wrow = p.ws + (static_cast<long long>(tile % p.split_k) * p.M + row) * p.N + n0;
@@ -701,22 +816,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             }
           }
         }
-      }
-      const bool staged = p.split_k == 1 && !p.direct_epilogue && !p.d_fp32 && !(p.aux != nullptr && p.aux_fp32) && (p.N & 7) == 0;
-      if (staged) {
-        uint8_t* st_out = epi_stage + (warp - 2) * 8192;
-        const int row_base = row - lane;
-        const bool has_aux = (p.aux != nullptr) && (p.act != 1);
-        uint4 areg[8];
-        if (has_aux) load_aux_group(p, areg, row_base, n0, aux_off, lane);
+        release_acc();
+      } else if (staged) {
 #pragma unroll 1
-        for (int c2 = 0; c2 < BN / 64; ++c2) {
-          if (n0 + c2 * 64 >= p.N) break;
-          const int next = (c2 + 1 < BN / 64 && n0 + (c2 + 1) * 64 < p.N) ? n0 + (c2 + 1) * 64 : -1;
-          epilogue_group_staged(p, taddr + c2 * 64, row_base, n0 + c2 * 64, d_off, aux_off, st_out, st_out + 4096, lane,
-                                areg, next);
+        for (int c2 = 0; c2 < num_groups; ++c2) {
+          epilogue_group_compute(p, et, taddr + c2 * 64, c2, num_groups, st_out, st_out + 4096, lane, areg);
+          if (c2 == num_groups - 1) release_acc();
+          epilogue_group_store(p, et, c2, st_out, st_out + 4096, lane);
         }
-      } else if (p.split_k == 1) {
+      } else {
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           uint32_t raw[32];
@@ -724,15 +832,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           tmem_ld_wait();
           epilogue_chunk(p, raw, row, n0 + c * 32, d_off, aux_off);
         }
-      }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (CG == 1 || leader) {
-          mbar_arrive(&tmem_empty[acc]);
-        } else {
-          mbar_arrive_cluster(&tmem_empty[acc], 0);
-        }
+        release_acc();
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
@@ -932,6 +1032,9 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   if (cg == 0) {
     const long long tiles_pair = 1LL * ((a->m + 255) / 256) * ((a->n + bn - 1) / bn) * bi * bo;
     cg = (bn == 256 && a->m >= 256 && (tiles_pair >= sms / 2 || can_split)) ? 2 : 1;
+    // short K (< 20 k-blocks): a tile's main loop is shorter than its epilogue and the pair's extra synchronisation no
+    // longer pays; measured at 8192x2304xK, 1-CTA 256-wide tiles win below K = 1280 (34.8 vs 37.6 us at K = 768)
+    if (cg == 2 && num_kb_total < 20 && !can_split) cg = 1;
   }
   DTB_REQUIRE(cg == 1 || (cg == 2 && bn == 256), "dtb_gemm_bf16: cta_pair=2 requires tile_n=256");
 
