@@ -198,15 +198,17 @@ bwd_param_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __re
   }
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-bwd_finish_kernel(const float* __restrict__ partial, int nparts, int cols, float* __restrict__ dgamma,
-                  float* __restrict__ dbeta, int accumulate) {
+bwd_finish_kernel(const float* __restrict__ partial, int nparts, int cols, T* __restrict__ dgamma,
+                  T* __restrict__ dbeta, int accumulate) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= 2 * cols) return;
   float s = 0.f;
   for (int p = 0; p < nparts; ++p) s += partial[static_cast<long long>(p) * 2 * cols + c];
-  float* dst = c < cols ? dgamma + c : dbeta + (c - cols);
-  *dst = accumulate ? *dst + s : s;
+  T* dst = c < cols ? dgamma + c : dbeta + (c - cols);
+  if (accumulate) s += static_cast<float>(*dst);
+  *dst = static_cast<T>(s);
 }
 
 }  // namespace ln
@@ -264,7 +266,37 @@ extern "C" int dtb_layernorm_bwd(const void* dy, const void* x, const void* gamm
   DTB_LAUNCH_OK();
   bwd_param_kernel<<<dim3((cols + 63) / 64, PARAM_CHUNKS), 256, 0, s>>>(DY, X, mean, rstd, scratch, rows, cols);
   DTB_LAUNCH_OK();
-  bwd_finish_kernel<<<(2 * cols + 255) / 256, 256, 0, s>>>(scratch, PARAM_CHUNKS, cols, dgamma, dbeta, accumulate_param_grads);
+  bwd_finish_kernel<float><<<(2 * cols + 255) / 256, 256, 0, s>>>(scratch, PARAM_CHUNKS, cols, dgamma, dbeta, accumulate_param_grads);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
+// Same, with dgamma / dbeta written as bf16 (straight into bf16 gradient buffers such as DDP bucket views: saves the
+// two cast launches per LayerNorm that the GPT-2 step used to make).
+extern "C" int dtb_layernorm_bwd_bf16grads(const void* dy, const void* x, const void* gamma, const float* mean,
+                                           const float* rstd, const void* dres_in, void* dx, void* dgamma, void* dbeta,
+                                           float* scratch, int rows, int cols, int accumulate_param_grads, void* stream) {
+  DTB_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 8 * 256,
+              "dtb_layernorm_bwd_bf16grads: cols=%d must be a multiple of 8 and <= 2048", cols);
+  DTB_REQUIRE(scratch != nullptr, "dtb_layernorm_bwd_bf16grads: scratch is required");
+  int grid = (rows + WARPS - 1) / WARPS;
+  const int cap = sm_count() * 8;
+  if (grid > cap) grid = cap;
+  auto s = static_cast<cudaStream_t>(stream);
+  const int nv = (cols / 8 + 31) / 32;
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto G = static_cast<const __nv_bfloat16*>(gamma);
+  auto DR = static_cast<const __nv_bfloat16*>(dres_in);
+  auto DX = static_cast<__nv_bfloat16*>(dx);
+  if (nv <= 4) bwd_dx_kernel<4><<<grid, WARPS * 32, 0, s>>>(DY, X, G, mean, rstd, DR, DX, rows, cols);
+  else bwd_dx_kernel<8><<<grid, WARPS * 32, 0, s>>>(DY, X, G, mean, rstd, DR, DX, rows, cols);
+  DTB_LAUNCH_OK();
+  bwd_param_kernel<<<dim3((cols + 63) / 64, PARAM_CHUNKS), 256, 0, s>>>(DY, X, mean, rstd, scratch, rows, cols);
+  DTB_LAUNCH_OK();
+  bwd_finish_kernel<__nv_bfloat16><<<(2 * cols + 255) / 256, 256, 0, s>>>(
+      scratch, PARAM_CHUNKS, cols, static_cast<__nv_bfloat16*>(dgamma), static_cast<__nv_bfloat16*>(dbeta),
+      accumulate_param_grads);
   DTB_LAUNCH_OK();
   return 0;
 }
@@ -356,7 +388,7 @@ extern "C" int dtb_layernorm_bwd_noalloc(const void* dy, const void* x, const vo
   DTB_LAUNCH_OK();
   bwd_param_kernel<<<dim3((cols + 63) / 64, PARAM_CHUNKS), 256, 0, s>>>(DY, X, mean, rstd, scratch, rows, cols);
   DTB_LAUNCH_OK();
-  bwd_finish_kernel<<<(2 * cols + 255) / 256, 256, 0, s>>>(scratch, PARAM_CHUNKS, cols, dgamma, dbeta,
+  bwd_finish_kernel<float><<<(2 * cols + 255) / 256, 256, 0, s>>>(scratch, PARAM_CHUNKS, cols, dgamma, dbeta,
                                                            accumulate_param_grads);
   DTB_LAUNCH_OK();
   return 0;

@@ -114,9 +114,8 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         ready(lin.weight, lin.bias)
 
     def ln_bwd(dy, x, ln: nn.LayerNorm, mean, rstd, dres, dx):
-        native.layernorm_bwd(dy, x, ln.weight, mean, rstd, dres, dx, ws["ln_dg"], ws["ln_db"], ws["ln_scratch"])
-        native.cast_f32_to_bf16(ws["ln_dg"], grad_of(ln.weight))
-        native.cast_f32_to_bf16(ws["ln_db"], grad_of(ln.bias))
+        native.layernorm_bwd_bf16grads(dy, x, ln.weight, mean, rstd, dres, dx, grad_of(ln.weight), grad_of(ln.bias),
+                                       ws["ln_scratch"])
         ready(ln.weight, ln.bias)
 
     # ------------------------------------------------------------------ forward

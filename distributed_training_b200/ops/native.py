@@ -313,6 +313,14 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dres_in, dx, dgamma, dbeta, scratch,
                                 _p(dbeta), _p(scratch), rows, cols, int(accumulate), _stream()))
 
 
+def layernorm_bwd_bf16grads(dy, x, gamma, mean, rstd, dres_in, dx, dgamma, dbeta, scratch, accumulate=False):
+    """``layernorm_bwd`` writing dgamma / dbeta as bf16 (no separate cast launches)."""
+    assert dgamma.dtype == torch.bfloat16 and dbeta.dtype == torch.bfloat16
+    rows, cols = x.numel() // x.shape[-1], x.shape[-1]
+    _ok(lib().dtb_layernorm_bwd_bf16grads(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres_in), _p(dx),
+                                          _p(dgamma), _p(dbeta), _p(scratch), rows, cols, int(accumulate), _stream()))
+
+
 def cross_entropy_fwd_bwd(logits, targets, row_loss, vocab, grad_scale, write_grad=True):
     rows, ld = logits.numel() // logits.shape[-1], logits.shape[-1]
     _ok(lib().dtb_cross_entropy_fwd_bwd(_p(logits), _p(targets), _p(row_loss), rows, vocab, C.c_longlong(ld),

@@ -123,6 +123,10 @@ int dtb_layernorm_bwd(const void* dy, const void* x, const void* gamma, const fl
                       const void* dres_in, void* dx, float* dgamma, float* dbeta, float* scratch, int rows, int cols,
                       int accumulate_param_grads, void* stream);
 
+/* dtb_layernorm_bwd with dgamma / dbeta written (or accumulated) as bf16, e.g. straight into bf16 gradient buckets. */
+int dtb_layernorm_bwd_bf16grads(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                                const void* dres_in, void* dx, void* dgamma, void* dbeta, float* scratch, int rows,
+                                int cols, int accumulate_param_grads, void* stream);
 /* Same computation as dtb_layernorm_bwd, for callers that cannot hand over a scratch buffer because they
  * cannot allocate device memory at all: a bare C/Fortran host with no device allocator, a plugin inside a
  * framework that owns the whole GPU and forbids cudaMalloc, or a loop that cannot tolerate cudaMalloc's

@@ -187,6 +187,25 @@ def test_layernorm_bwd(rows, cols):
     assert torch.allclose(dbeta, br.grad, atol=2e-2 * math.sqrt(rows), rtol=1e-2)
 
 
+def test_layernorm_bwd_bf16_param_grads_match_fp32_path():
+    rows, cols = 1024, 768
+    x, dy = _bf16(rows, cols, seed=1), _bf16(rows, cols, seed=2)
+    g, b = _bf16(cols, seed=3) * 0.1 + 1, _bf16(cols, seed=4) * 0.1
+    y = torch.empty_like(x)
+    mean, rstd = torch.empty(rows, device=DEV), torch.empty(rows, device=DEV)
+    native.layernorm_fwd(x, None, g, b, y, None, mean, rstd)
+    scratch = torch.empty(native.layernorm_bwd_scratch_floats(rows, cols), device=DEV)
+    dx32, dg32, db32 = torch.empty_like(x), torch.empty(cols, device=DEV), torch.empty(cols, device=DEV)
+    native.layernorm_bwd(dy, x, g, mean, rstd, None, dx32, dg32, db32, scratch)
+    dx16 = torch.empty_like(x)
+    dg16, db16 = torch.empty(cols, device=DEV, dtype=torch.bfloat16), torch.empty(cols, device=DEV, dtype=torch.bfloat16)
+    native.layernorm_bwd_bf16grads(dy, x, g, mean, rstd, None, dx16, dg16, db16, scratch)
+    assert torch.equal(dx16, dx32)
+    assert torch.equal(dg16, dg32.to(torch.bfloat16)) and torch.equal(db16, db32.to(torch.bfloat16))
+    native.layernorm_bwd_bf16grads(dy, x, g, mean, rstd, None, dx16, dg16, db16, scratch, accumulate=True)
+    assert torch.allclose(dg16.float(), 2 * dg32, rtol=2e-2, atol=1e-2)
+
+
 # ------------------------------------------------------------------------ losses
 @pytest.mark.parametrize("rows,vocab,ld", [(256, 8192, 8192), (64, 50257, 50304), (33, 1000, 1000)])
 def test_cross_entropy_fused(rows, vocab, ld):
