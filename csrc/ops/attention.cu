@@ -34,6 +34,14 @@ constexpr int TQ = 128, TK = 128, HD = 64;
 constexpr int TILE_BYTES = 128 * 64 * 2;   // 16 KB: a [128 x 64] bf16 tile
 constexpr float LOG2E = 1.4426950408889634f;
 
+// 2^x on the SFU, flush-to-zero: exp2f() without -use_fast_math expands to a range check, a pre-scale and a
+// post-square around MUFU.EX2 (4 instructions per score; ncu showed the softmax warps issue-bound)
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -164,32 +172,55 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
       tmem_ld_32x32b_x32(tmem_row + cc * 32, chunk);
     }
     tmem_ld_wait();
+    // Only the diagonal tile needs the causal mask; every other tile of this row block is fully visible, and a
+    // per-element predicate there cost 40 % of the kernel's instructions (ISETP / PLOP3 / FSEL in the ncu source view).
     const bool diag = (j == qt);
     float tile_max = -INFINITY;
+    if (diag) {
 #pragma unroll
-    for (int e = 0; e < 128; ++e) {
-      const float sc = __uint_as_float(sv[e]);
-      if (!diag || e <= tid) tile_max = fmaxf(tile_max, sc);
+      for (int e = 0; e < 128; ++e)
+        if (e <= tid) tile_max = fmaxf(tile_max, __uint_as_float(sv[e]));
+    } else {
+#pragma unroll
+      for (int e = 0; e < 128; ++e) tile_max = fmaxf(tile_max, __uint_as_float(sv[e]));
     }
     const float m_new = fmaxf(m, tile_max);
-    const float alpha = exp2f((m - m_new) * c);
+    const float alpha = fast_exp2((m - m_new) * c);
     const float mc = m_new * c;
     float rowsum = 0.f;
+    if (diag) {
 #pragma unroll
-    for (int q = 0; q < 16; ++q) {
-      float p[8];
+      for (int q = 0; q < 16; ++q) {
+        float p[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int col = q * 8 + e;
-        p[e] = (!diag || col <= tid) ? exp2f(fmaf(__uint_as_float(sv[col]), c, -mc)) : 0.f;
-        rowsum += p[e];
+        for (int e = 0; e < 8; ++e) {
+          const int col = q * 8 + e;
+          p[e] = (col <= tid) ? fast_exp2(fmaf(__uint_as_float(sv[col]), c, -mc)) : 0.f;
+          rowsum += p[e];
+        }
+        uint4 pk;
+        pk.x = pack2(p[0], p[1]);
+        pk.y = pack2(p[2], p[3]);
+        pk.z = pack2(p[4], p[5]);
+        pk.w = pack2(p[6], p[7]);
+        *reinterpret_cast<uint4*>(sP + swz_chunk(tid, q)) = pk;
       }
-      uint4 pk;
-      pk.x = pack2(p[0], p[1]);
-      pk.y = pack2(p[2], p[3]);
-      pk.z = pack2(p[4], p[5]);
-      pk.w = pack2(p[6], p[7]);
-      *reinterpret_cast<uint4*>(sP + swz_chunk(tid, q)) = pk;
+    } else {
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        float p[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          p[e] = fast_exp2(fmaf(__uint_as_float(sv[q * 8 + e]), c, -mc));
+          rowsum += p[e];
+        }
+        uint4 pk;
+        pk.x = pack2(p[0], p[1]);
+        pk.y = pack2(p[2], p[3]);
+        pk.z = pack2(p[4], p[5]);
+        pk.w = pack2(p[6], p[7]);
+        *reinterpret_cast<uint4*>(sP + swz_chunk(tid, q)) = pk;
+      }
     }
     l = l * alpha + rowsum;
     m = m_new;
@@ -396,11 +427,18 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       tmem_ld_32x32b_x32(tmem_row + T_DP + cc * 32, vd);
       tmem_ld_wait();
       float p[32], ds[32];
+      if (diag) {     // causal mask on the diagonal tile only (uniform branch, see the forward kernel)
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const bool keep = !diag || (cc * 32 + e <= tid);
-        p[e] = keep ? exp2f(fmaf(__uint_as_float(vs[e]), c, -row_lse)) : 0.f;
-        ds[e] = p[e] * (__uint_as_float(vd[e]) - row_delta) * scale;
+        for (int e = 0; e < 32; ++e) {
+          p[e] = (cc * 32 + e <= tid) ? fast_exp2(fmaf(__uint_as_float(vs[e]), c, -row_lse)) : 0.f;
+          ds[e] = p[e] * (__uint_as_float(vd[e]) - row_delta) * scale;
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          p[e] = fast_exp2(fmaf(__uint_as_float(vs[e]), c, -row_lse));
+          ds[e] = p[e] * (__uint_as_float(vd[e]) - row_delta) * scale;
+        }
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
