@@ -43,6 +43,25 @@ class _FusedBase(torch.optim.Optimizer):
     def _pending(self, group) -> List[torch.Tensor]:
         return [p for p in group["params"] if p.grad is not None and id(p) not in self._already_updated]
 
+    @torch.no_grad()
+    def step_params(self, params) -> None:
+        """Apply THIS step's update to ``params`` now, on the current stream; the following ``step()`` skips them.
+
+        The data-parallel wrapper calls this per gradient bucket right behind the bucket's all-reduce, so the
+        optimizer runs under the rest of backward instead of after it (the reference steps the whole model after
+        ``loss.backward()``, /root/reference/src/distributed_trainer.py:164-165)."""
+        wanted = {id(p) for p in params if p.grad is not None} - self._already_updated
+        if not wanted:
+            return
+        for group in self.param_groups:
+            chosen = [p for p in group["params"] if id(p) in wanted]
+            if chosen:
+                self._apply(group, chosen, self._step_count + 1)
+        self._already_updated.update(wanted)
+
+    def _apply(self, group, params: List[torch.Tensor], t: int) -> None:  # pragma: no cover - interface
+        raise NotImplementedError
+
     def zero_grad(self, set_to_none: bool = False) -> None:  # keep bucket views attached
         if set_to_none:
             return super().zero_grad(set_to_none=True)
@@ -75,46 +94,48 @@ class FusedSGD(_FusedBase):
     def step(self, closure=None):
         loss = closure() if closure is not None else None
         self._step_count += 1
-        native = _native()
         for group in self.param_groups:
-            lr, mom, wd = group["lr"], group["momentum"], group["weight_decay"]
             params = self._pending(group)
-            if not params:
-                continue
-            grads = [p.grad for p in params]
-            if native is not None and params[0].is_cuda:
-                bufs = None
-                if mom != 0.0:
-                    bufs = []
-                    for p in params:
-                        st = self.state[p]
-                        if "momentum_buffer" not in st:
-                            st["momentum_buffer"] = torch.zeros_like(p, dtype=torch.float32)
-                        bufs.append(st["momentum_buffer"])
-                masters = [self._master(p) for p in params] if self.master_weights else None
-                native.multi_tensor_sgd(params, grads, masters, bufs, lr, mom, wd)
-                continue
-            # reference math on CPU
-            targets = [self._master(p) if self._master(p) is not None else p for p in params]
-            g32 = [g.to(t.dtype) for g, t in zip(grads, targets)]
-            if wd != 0.0:
-                g32 = torch._foreach_add(g32, targets, alpha=wd)
-            if mom != 0.0:
-                bufs = []
-                for p, g in zip(params, g32):
-                    st = self.state[p]
-                    if "momentum_buffer" not in st:
-                        st["momentum_buffer"] = torch.zeros_like(g)
-                    bufs.append(st["momentum_buffer"])
-                torch._foreach_mul_(bufs, mom)
-                torch._foreach_add_(bufs, g32)
-                g32 = bufs
-            torch._foreach_add_(targets, g32, alpha=-lr)
-            for p, t in zip(params, targets):
-                if t is not p:
-                    p.copy_(t)
+            if params:
+                self._apply(group, params, self._step_count)
         self._already_updated.clear()
         return loss
+
+    def _apply(self, group, params: List[torch.Tensor], t: int) -> None:
+        native = _native()
+        lr, mom, wd = group["lr"], group["momentum"], group["weight_decay"]
+        grads = [p.grad for p in params]
+        if native is not None and params[0].is_cuda:
+            bufs = None
+            if mom != 0.0:
+                bufs = []
+                for p in params:
+                    st = self.state[p]
+                    if "momentum_buffer" not in st:
+                        st["momentum_buffer"] = torch.zeros_like(p, dtype=torch.float32)
+                    bufs.append(st["momentum_buffer"])
+            masters = [self._master(p) for p in params] if self.master_weights else None
+            native.multi_tensor_sgd(params, grads, masters, bufs, lr, mom, wd)
+            return
+        # reference math on CPU
+        targets = [self._master(p) if self._master(p) is not None else p for p in params]
+        g32 = [g.to(t_.dtype) for g, t_ in zip(grads, targets)]
+        if wd != 0.0:
+            g32 = torch._foreach_add(g32, targets, alpha=wd)
+        if mom != 0.0:
+            bufs = []
+            for p, g in zip(params, g32):
+                st = self.state[p]
+                if "momentum_buffer" not in st:
+                    st["momentum_buffer"] = torch.zeros_like(g)
+                bufs.append(st["momentum_buffer"])
+            torch._foreach_mul_(bufs, mom)
+            torch._foreach_add_(bufs, g32)
+            g32 = bufs
+        torch._foreach_add_(targets, g32, alpha=-lr)
+        for p, t_ in zip(params, targets):
+            if t_ is not p:
+                p.copy_(t_)
 
 
 class FusedAdamW(_FusedBase):
@@ -136,33 +157,35 @@ class FusedAdamW(_FusedBase):
     def step(self, closure=None):
         loss = closure() if closure is not None else None
         self._step_count += 1
-        t = self._step_count
-        native = _native()
         for group in self.param_groups:
-            lr, (b1, b2), eps, wd = group["lr"], group["betas"], group["eps"], group["weight_decay"]
-            params = [p for p in group["params"] if p.grad is not None]
-            if not params:
-                continue
-            grads = [p.grad for p in params]
-            ms, vs = zip(*[self._moments(p) for p in params])
-            masters = [self._master(p) for p in params]
-            bc1, bc2 = 1.0 - b1 ** t, 1.0 - b2 ** t
-            if native is not None and params[0].is_cuda:
-                native.multi_tensor_adamw(params, grads, list(ms), list(vs),
-                                          masters if self.master_weights else None,
-                                          lr, b1, b2, eps, wd, bc1, bc2)
-                continue
-            for p, g, m, v, w in zip(params, grads, ms, vs, masters):
-                target = w if w is not None else p
-                g32 = g.float()
-                m.mul_(b1).add_(g32, alpha=1.0 - b1)
-                v.mul_(b2).addcmul_(g32, g32, value=1.0 - b2)
-                x = target.float() if target.dtype != torch.float32 else target
-                x = x * (1.0 - lr * wd) - (lr / bc1) * m / ((v / bc2).sqrt() + eps)
-                target.copy_(x)
-                if w is not None:
-                    p.copy_(w)
+            params = self._pending(group)
+            if params:
+                self._apply(group, params, self._step_count)
+        self._already_updated.clear()
         return loss
+
+    def _apply(self, group, params: List[torch.Tensor], t: int) -> None:
+        native = _native()
+        lr, (b1, b2), eps, wd = group["lr"], group["betas"], group["eps"], group["weight_decay"]
+        grads = [p.grad for p in params]
+        ms, vs = zip(*[self._moments(p) for p in params])
+        masters = [self._master(p) for p in params]
+        bc1, bc2 = 1.0 - b1 ** t, 1.0 - b2 ** t
+        if native is not None and params[0].is_cuda:
+            native.multi_tensor_adamw(params, grads, list(ms), list(vs),
+                                      masters if self.master_weights else None,
+                                      lr, b1, b2, eps, wd, bc1, bc2)
+            return
+        for p, g, m, v, w in zip(params, grads, ms, vs, masters):
+            target = w if w is not None else p
+            g32 = g.float()
+            m.mul_(b1).add_(g32, alpha=1.0 - b1)
+            v.mul_(b2).addcmul_(g32, g32, value=1.0 - b2)
+            x = target.float() if target.dtype != torch.float32 else target
+            x = x * (1.0 - lr * wd) - (lr / bc1) * m / ((v / bc2).sqrt() + eps)
+            target.copy_(x)
+            if w is not None:
+                p.copy_(w)
 
 
 def build_fused_optimizer(params: List[torch.Tensor], spec: OptimizerSpec,

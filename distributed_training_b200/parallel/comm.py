@@ -85,6 +85,15 @@ class Communicator(ABC):
         """Hint: the next allocations total ``nbytes`` and should be co-located."""
         return None
 
+    def then(self, work: Optional["Work"], fn) -> Optional["Work"]:
+        """Run ``fn()`` after ``work`` (a collective handle or None) and return a handle for both.  Stream-ordered
+        communicators run it on their communication stream so it overlaps the caller's compute; this default just
+        waits and calls."""
+        if work is not None:
+            work.wait()
+        fn()
+        return None
+
     def all_reduce_max_scalar(self, value: float) -> float:
         """Max of a host scalar over ranks (timing: max over ranks)."""
         if self.world_size == 1 or not dist.is_initialized():

@@ -210,7 +210,27 @@ class ReplicatedModule(nn.Module):
                 self._optimizer.mark_updated(self._params[i] for i in bucket.plan.param_indices)
             else:
                 bucket.work = self.comm.all_reduce_avg_(bucket.buffer)
+                self._step_behind(bucket, [self._params[i] for i in bucket.plan.param_indices])
+        elif self._in_manual_step:
+            self._step_behind(bucket, [self._params[i] for i in bucket.plan.param_indices])
         bucket.launched = True
+
+    def _step_behind(self, bucket: GradBucket, params: List[nn.Parameter]) -> None:
+        """Stateful optimizers (AdamW, SGD with momentum / master weights) cannot be folded into the reduction kernel,
+        but their update of a bucket can run right behind that bucket's all-reduce on the communication stream, under
+        the rest of backward, instead of as one pass over the whole model afterwards.  Native models only: they mark a
+        parameter ready after its last use in backward, so nothing reads the old value any more."""
+        opt = self._optimizer
+        if getattr(opt, "fusable_sgd", False):
+            return          # stateless SGD: fused into the reduction / wgrad epilogue; leftovers are one tiny launch
+        if (opt is None or not self._in_manual_step or not hasattr(opt, "step_params") or not self.params_in_heap
+                or any(self._bucket_of[self._index_of[id(p)]].views[self._index_of[id(p)]].dtype != p.dtype
+                       for p in params)):
+            return
+        for p in params:       # gradients live in the bucket views
+            if p.grad is None:
+                p.grad = self._bucket_of[self._index_of[id(p)]].views[self._index_of[id(p)]]
+        bucket.work = self.comm.then(bucket.work, lambda: opt.step_params(params))
 
     def _finalize_backward(self) -> None:
         self._callback_queued = False
@@ -264,6 +284,8 @@ class ReplicatedModule(nn.Module):
             bucket.ready.add(i)
             bucket.pending = 0
             bucket.launched = True
+            if hyper is None:
+                self._step_behind(bucket, [param])
 
     def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, **kwargs: Any) -> torch.Tensor:
         """One fused forward+backward of a native model with overlapped reduction."""

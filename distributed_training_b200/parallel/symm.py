@@ -257,6 +257,17 @@ class SymmComm(Communicator):
             event.record()
         return _StreamWork(event)
 
+    def then(self, work: Optional[Work], fn) -> Optional[Work]:
+        """``fn()`` on the communication stream, behind ``work`` (same stream) and everything already queued on the
+        caller's stream; e.g. the optimizer update of a bucket right after its all-reduce."""
+        if self.stream is None:
+            return super().then(work, fn)
+        with self._on_comm_stream():
+            fn()
+            event = torch.cuda.Event()
+            event.record()
+        return _StreamWork(event)
+
     def all_reduce_sgd_(self, grads: torch.Tensor, params: torch.Tensor, lr: float, weight_decay: float) -> Work:
         """Average ``grads`` over ranks and apply ``p = p*(1-lr*wd) - lr*g`` to ``params`` (same layout, both in
         the same heap segment) in one kernel; every rank ends with identical new parameters."""

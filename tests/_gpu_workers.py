@@ -121,31 +121,37 @@ def ddp_native(rank, world, port, out_dir):
     _init(rank, world, port)
     strategy = DDPStrategy(rank, True)
     try:
-      for fused in (False, True, "chunked"):
-        if fused == "chunked":   # every parameter in its own bucket + chunked reduction of the last wgrad
+      for fused in (False, True, "chunked", "adamw", "adamw_chunked"):
+        adamw = str(fused).startswith("adamw")   # stateful optimizer: stepped per bucket behind its all-reduce
+        if str(fused).endswith("chunked"):   # every parameter in its own bucket + chunked reduction of the last wgrad
             strategy = DDPStrategy(rank, True, comm=strategy.comm, bucket_cap_mb=0.01, first_bucket_mb=0.001)
         torch.manual_seed(100 + rank)                        # rank-dependent init: must be broadcast
         model = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16).cuda()
         wrapped = strategy.prepare_model(model, rank)
         assert wrapped.native_step
-        if fused == "chunked":
+        if str(fused).endswith("chunked"):
             wrapped.TAIL_CHUNK_MIN_BYTES = 0
             assert wrapped.tail_chunks(model.layers[0].weight) == 4
-        opt = strategy.build_optimizer(wrapped, OptimizerSpec("sgd", lr=0.05, weight_decay=0.01))
+        spec = (OptimizerSpec("adamw", lr=2e-3, weight_decay=0.01) if adamw else
+                OptimizerSpec("sgd", lr=0.05, weight_decay=0.01))
+        opt = strategy.build_optimizer(wrapped, spec)
         if fused:
             wrapped.attach_optimizer(opt)                    # gradient all-reduce + SGD in one kernel
-            assert wrapped._fused_sgd_hyper() is not None
+            assert adamw or wrapped._fused_sgd_hyper() is not None
         torch.manual_seed(100)
         ref = MLP(256, 512, 384, num_layers=3, dtype=torch.bfloat16)
         ref = ref.float().cuda()
         for (k1, v1), (k2, v2) in zip(wrapped.state_dict().items(), ref.state_dict().items()):
             assert k1 == "module." + k2 and torch.equal(v1.float(), v2), k1
-        ropt = torch.optim.SGD(ref.parameters(), lr=0.05, weight_decay=0.01)
+        ropt = (torch.optim.AdamW(ref.parameters(), lr=2e-3, weight_decay=0.01) if adamw else
+                torch.optim.SGD(ref.parameters(), lr=0.05, weight_decay=0.01))
         g = torch.Generator().manual_seed(9)
         for step in range(4):
             x = torch.randn(world * 128, 256, generator=g).to(torch.bfloat16).cuda()
             y = torch.randint(0, 384, (world * 128,), generator=g).cuda()
             loss = wrapped.forward_backward(x[rank * 128:(rank + 1) * 128], y[rank * 128:(rank + 1) * 128])
+            if adamw:    # every parameter was already stepped behind its bucket's all-reduce
+                assert not any(opt._pending(grp) for grp in opt.param_groups), "step-behind path did not run"
             opt.step()
             ropt.zero_grad()
             rl = F.cross_entropy(ref(x.float()), y)
