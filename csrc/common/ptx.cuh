@@ -112,6 +112,18 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
   } while (!done);
 }
 
+// Asynchronous store of one word to the same shared-memory offset in CTA `cta_rank` of the cluster, completing 4 bytes
+// of transaction count on that CTA's mbarrier at `bar`'s offset.  The data is visible to whoever observes the phase
+// completion, exactly like a TMA load -- no cluster-scope fence on either side (an acquire.cluster wait makes ptxas
+// emit CCTL.IVALL + ERRBAR, which drains every outstanding store of the waiting warp).
+__device__ __forceinline__ void st_async_cluster_u32(void* local_ptr, uint64_t* bar, uint32_t cta_rank, uint32_t value) {
+  uint32_t raddr, rbar;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(local_ptr)), "r"(cta_rank));
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(smem_u32(bar)), "r"(cta_rank));
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(raddr), "r"(value), "r"(rbar)
+               : "memory");
+}
+
 // store a word at the same shared-memory offset of another CTA in the cluster
 __device__ __forceinline__ void st_shared_cluster_u32(void* local_ptr, uint32_t cta_rank, uint32_t value) {
   uint32_t remote;

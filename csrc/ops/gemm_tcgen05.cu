@@ -497,19 +497,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   const uint32_t tmem_base = *tmem_ptr;
 
   // Consumer side of the tile ring (dynamic scheduling): the j-th published tile id of this cluster.  Called by whole
-  // warps; one lane tells the leader CTA that this warp is done with the slot.
+  // warps.  The id arrives by st.async (data + 4 bytes of transaction count on this CTA's sched_full barrier), so a
+  // plain CTA-scope wait is enough; `arm` = this warp is the one that posts the barrier's single arrival + expect_tx for
+  // the phase (the TMA warp of each CTA).  One lane then tells the leader CTA that this warp is done with the slot.
   const bool dyn = !GATHER && p.sched != nullptr;
-  auto next_tile = [&](int tile, int& j) -> int {
+  auto next_tile = [&](int tile, int& j, bool arm) -> int {
     if (!dyn) return tile + num_clusters;
     const int slot = j & (SCHED_DEPTH - 1);
-    mbar_wait_cluster(&sched_full[slot], (j / SCHED_DEPTH) & 1);
+    if (arm && lane == 0) mbar_arrive_expect_tx(&sched_full[slot], 4);
+    mbar_wait(&sched_full[slot], (j / SCHED_DEPTH) & 1);
     const int t = *reinterpret_cast<volatile int*>(&sched_tile[slot]);
     __syncwarp();
-    if (lane == 0) {
+    // the predicate depends on the loaded value, so the arrive cannot be issued before the read has returned
+    if (lane == 0 && t >= 0) {
       if (CG == 1 || leader) {
         mbar_arrive(&sched_empty[slot]);
       } else {
-        mbar_arrive_cluster(&sched_empty[slot], 0);
+        mbar_arrive_remote(&sched_empty[slot], 0);
       }
     }
     ++j;
@@ -531,16 +535,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     auto publish = [&]() -> int {
       const int nxt = __shfl_sync(0xffffffffu, fetched, 0);
       const int slot = published & (SCHED_DEPTH - 1);
-      mbar_wait_cluster(&sched_empty[slot], ((published / SCHED_DEPTH) & 1) ^ 1);
+      mbar_wait(&sched_empty[slot], ((published / SCHED_DEPTH) & 1) ^ 1);
       if (lane == 0) {
         // every cluster fetches until it is handed a unit past the end: num_tiles + num_clusters fetches per launch
         if (nxt == num_tiles + num_clusters - 1) atomicExch(p.sched, 0);
-        *reinterpret_cast<volatile int*>(&sched_tile[slot]) = nxt;
-        mbar_arrive(&sched_full[slot]);
-        if constexpr (CG == 2) {
-          st_shared_cluster_u32(&sched_tile[slot], 1, static_cast<uint32_t>(nxt));
-          mbar_arrive_cluster(&sched_full[slot], 1);
-        }
+        mbar_arrive_expect_tx(&sched_full[slot], 4);          // this CTA's arrival for the phase
+#pragma unroll
+        for (uint32_t r = 0; r < static_cast<uint32_t>(CG); ++r)
+          st_async_cluster_u32(&sched_tile[slot], &sched_full[slot], r, static_cast<uint32_t>(nxt));
       }
       __syncwarp();
       ++published;
@@ -551,7 +553,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       if (lane == 0) fetched = atomicAdd(p.sched, 1);   // held by another kernel) finds only what is still undone
       tile = publish();
     } else if (dyn) {
-      tile = next_tile(0, consumed);
+      tile = next_tile(0, consumed, true);
     }
     while (tile < num_tiles) {
       bool pending = false;
@@ -626,7 +628,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
       }
       if (pending) following = publish();
-      tile = scheduler ? following : next_tile(tile, consumed);
+      tile = scheduler ? following : next_tile(tile, consumed, true);
     }
   } else if (warp == 1) {
     // ============================= MMA issuer =============================
@@ -647,7 +649,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       int acc = 0;
       uint32_t acc_phase = 0;
       int consumed = 0;
-      for (int tile = dyn ? next_tile(0, consumed) : cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
+      for (int tile = dyn ? next_tile(0, consumed, false) : cluster_id; tile < num_tiles;
+           tile = next_tile(tile, consumed, false)) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -744,7 +747,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     int acc = 0;
     uint32_t acc_phase = 0;
     int consumed = 0;
-    for (int tile = dyn ? next_tile(0, consumed) : cluster_id; tile < num_tiles; tile = next_tile(tile, consumed)) {
+    for (int tile = dyn ? next_tile(0, consumed, false) : cluster_id; tile < num_tiles;
+         tile = next_tile(tile, consumed, false)) {
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
       const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
@@ -1032,9 +1036,9 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   if (cg == 0) {
     const long long tiles_pair = 1LL * ((a->m + 255) / 256) * ((a->n + bn - 1) / bn) * bi * bo;
     cg = (bn == 256 && a->m >= 256 && (tiles_pair >= sms / 2 || can_split)) ? 2 : 1;
-    // short K (< 20 k-blocks): a tile's main loop is shorter than its epilogue and the pair's extra synchronisation no
-    // longer pays; measured at 8192x2304xK, 1-CTA 256-wide tiles win below K = 1280 (34.8 vs 37.6 us at K = 768)
-    if (cg == 2 && num_kb_total < 20 && !can_split) cg = 1;
+    // very short K (< 8 k-blocks): the pair's extra synchronisation no longer pays; measured at 8192x2304xK, 1-CTA
+    // 256-wide tiles win at K = 64 / 256 (24.6 vs 26.6, 27.4 vs 29.5 us) and lose from K = 768 up (35.5 vs 33.6 us)
+    if (cg == 2 && num_kb_total < 8 && !can_split) cg = 1;
   }
   DTB_REQUIRE(cg == 1 || (cg == 2 && bn == 256), "dtb_gemm_bf16: cta_pair=2 requires tile_n=256");
 
