@@ -38,7 +38,8 @@ struct Params {
   int M, N, K;
   int batch_inner, batch;        // batch = inner * outer
   int m_blocks, n_blocks;        // in units of (CG*BM) x BN tiles
-  int group_m;
+  int group_m, group_m_log2;     // rasterisation group (power of two)
+  float rcp_per_batch, rcp_group_size;   // reciprocals for div_small (host guarantees < 2^22 work units)
   void* d;
   void* d2;
   const void* aux;
@@ -149,23 +150,44 @@ __device__ __forceinline__ void add_bias32(const Params& p, float (&v)[32], int 
   }
 }
 
+// n / d for 0 <= n < 2^22 with rcp = 1.0f / d: the float estimate is off by at most one.  A runtime integer division is
+// ~35 dependent instructions; tile_coords used five of them per tile in every warp role, which the ncu source view
+// showed as 43 % of the epilogue warps' time in an epilogue-bound (short-K) GEMM.
+__device__ __forceinline__ int div_small(int n, int d, float rcp) {
+  int q = __float2int_rz(__int2float_rz(n) * rcp);
+  const int r = n - q * d;
+  q += (r >= d) ? 1 : 0;
+  q -= (r < 0) ? 1 : 0;
+  return q;
+}
+
 __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& bi, int& m_blk, int& n_blk) {
-  tile /= p.split_k;      // consecutive work units are the K-splits of one output tile
+  if (p.split_k > 1) tile /= p.split_k;      // consecutive work units are the K-splits of one output tile
   const int per_batch = p.m_blocks * p.n_blocks;
-  bi = tile / per_batch;
-  int t = tile - bi * per_batch;
+  bi = 0;
+  int t = tile;
+  if (p.batch > 1) {
+    bi = div_small(tile, per_batch, p.rcp_per_batch);
+    t = tile - bi * per_batch;
+  }
   if (p.g_rotate >= 0) {   // all m-blocks of one n-block, n-blocks starting at this rank's own rows
-    m_blk = t % p.m_blocks;
-    n_blk = (t / p.m_blocks + p.g_rotate) % p.n_blocks;
+    const int q = t / p.m_blocks;
+    m_blk = t - q * p.m_blocks;
+    n_blk = (q + p.g_rotate) % p.n_blocks;
     return;
   }
   const int group_size = p.group_m * p.n_blocks;
-  const int group_id = t / group_size;
+  const int group_id = div_small(t, group_size, p.rcp_group_size);
   const int first_m = group_id * p.group_m;
-  const int gm = min(p.m_blocks - first_m, p.group_m);
   const int in_group = t - group_id * group_size;
-  m_blk = first_m + in_group % gm;
-  n_blk = in_group / gm;
+  if (p.m_blocks - first_m >= p.group_m) {     // full group: group_m is a power of two
+    m_blk = first_m + (in_group & (p.group_m - 1));
+    n_blk = in_group >> p.group_m_log2;
+  } else {
+    const int gm = p.m_blocks - first_m;
+    n_blk = in_group / gm;
+    m_blk = first_m + in_group - n_blk * gm;
+  }
 }
 
 // Epilogue for one 32-column chunk of one row.
@@ -564,7 +586,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
-      const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
+      int b_in = 0, b_out = 0;
+      if (p.batch > 1) {
+        b_out = bi / p.batch_inner;
+        b_in = bi - b_out * p.batch_inner;
+      }
       const int m0 = (m_blk * CG + static_cast<int>(cta_rank)) * BM;
       const int n0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;
       if constexpr (GATHER) {
@@ -576,7 +602,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
         asm volatile("fence.proxy.async.global;" ::: "memory");
       }
-      const int kb_lo = (tile % p.split_k) * p.kb_per_split;
+      const int kb_lo = p.split_k > 1 ? (tile % p.split_k) * p.kb_per_split : 0;
       const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
       for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -654,7 +680,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
-        const int kb_lo = (tile % p.split_k) * p.kb_per_split;
+        const int kb_lo = p.split_k > 1 ? (tile % p.split_k) * p.kb_per_split : 0;
         const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&full_bar[stage], phase);
@@ -751,9 +777,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
          tile = next_tile(tile, consumed, false)) {
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
-      const int b_in = bi % p.batch_inner, b_out = bi / p.batch_inner;
-      const long long d_off = b_in * p.d_si + b_out * p.d_so;
-      const long long aux_off = b_in * p.aux_si + b_out * p.aux_so;
+      long long d_off = 0, aux_off = 0;
+      if (p.batch > 1) {
+        const int b_out = bi / p.batch_inner, b_in = bi - b_out * p.batch_inner;
+        d_off = b_in * p.d_si + b_out * p.d_so;
+        aux_off = b_in * p.aux_si + b_out * p.aux_so;
+      }
       const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BM + quad * 32 + lane;
       const int n0 = n_blk * BN;
       // ---- per-tile setup, done BEFORE waiting for the accumulator so that the global loads issued here (bias, first
@@ -1070,6 +1099,10 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   p.m_blocks = (a->m + BM * cg - 1) / (BM * cg);
   p.n_blocks = (a->n + bn - 1) / bn;
   p.group_m = cg == 2 ? 8 : 16;
+  p.group_m_log2 = cg == 2 ? 3 : 4;
+  p.rcp_per_batch = 1.0f / static_cast<float>(p.m_blocks * p.n_blocks);
+  p.rcp_group_size = 1.0f / static_cast<float>(p.group_m * p.n_blocks);
+  DTB_REQUIRE(1LL * p.m_blocks * p.n_blocks * bi * bo < (1LL << 22), "dtb_gemm_bf16: more than 4M output tiles");
   p.d = a->d; p.d2 = a->d2; p.aux = a->aux; p.bias = a->bias;
   p.ldd = a->ldd; p.ld_aux = a->ld_aux;
   p.d_si = a->d_stride_inner; p.d_so = a->d_stride_outer;
