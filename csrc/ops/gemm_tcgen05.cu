@@ -69,6 +69,9 @@ struct Params {
   // co-resident communication CTA ends up doing fewer tiles and a cluster whose SMs are held by another kernel joins
   // late (or not at all).  nullptr = static round-robin.  The last fetch of a launch resets the counter to zero.
   int* sched;
+  // ---- TMA-store epilogue: [32 rows x 64 cols] boxes of D (and D2) with the staging buffers' 128-byte swizzle
+  int tma_store;
+  CUtensorMap map_d, map_d2;
 };
 
 constexpr int SCHED_DEPTH = 4;       // ring of published tile ids per CTA
@@ -308,6 +311,7 @@ struct EpiTile {
   long long step_d;      // bytes between rows r and r + 4 of D / D2
   long long step_aux;
   int row_base, n0;
+  int b_in, b_out;       // batch coordinates (TMA-store path)
   bool interior;         // all 32 rows and all BN columns are in range
   bool bias_regs;        // bias for the whole tile is held across the warp in `bias` (lane l: columns 8l .. 8l+7)
   uint4 bias;
@@ -455,11 +459,26 @@ __device__ __forceinline__ void epilogue_group_store(const Params& p, const EpiT
   __syncwarp();
 }
 
+// Same hand-off through the TMA unit: one elected lane issues a bulk tensor store of the [32 x 64] box (and of the
+// pre-activation box).  The warps' LSU work per group drops from 8 x (LDS + STG) per lane to nothing, edges are clipped
+// by the tensor map, and the store overlaps the next group's TMEM reads.
+__device__ __forceinline__ void epilogue_group_store_tma(const Params& p, const EpiTile& t, int c2, const uint8_t* st_out,
+                                                         const uint8_t* st_in, int lane) {
+  fence_proxy_async_smem();      // every lane: my st.shared results are visible to the async proxy
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_4d(&p.map_d, st_out, t.n0 + c2 * 64, t.row_base, t.b_in, t.b_out);
+    if (p.act == 1 && t.out2 != nullptr) tma_store_4d(&p.map_d2, st_in, t.n0 + c2 * 64, t.row_base, t.b_in, t.b_out);
+    tma_store_commit();
+  }
+}
+
 constexpr int NUM_GATHER_WARPS = 2;
 
 template <int CG, int BN, int A_MN, int B_MN, bool GATHER = false>
 __global__ void __launch_bounds__(NUM_THREADS + (GATHER ? 32 * NUM_GATHER_WARPS : 0), 1)
-gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Params p) {
+gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+            const __grid_constant__ Params p) {
   using Cfg = Config<CG, BN>;
   constexpr int STAGES = Cfg::STAGES;
 
@@ -773,13 +792,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     int acc = 0;
     uint32_t acc_phase = 0;
     int consumed = 0;
+    int store_groups = 0;        // bulk-store groups issued by this warp (TMA-store epilogue)
     for (int tile = dyn ? next_tile(0, consumed, false) : cluster_id; tile < num_tiles;
          tile = next_tile(tile, consumed, false)) {
       int bi, m_blk, n_blk;
       tile_coords(p, tile, bi, m_blk, n_blk);
       long long d_off = 0, aux_off = 0;
+      int b_in = 0, b_out = 0;
       if (p.batch > 1) {
-        const int b_out = bi / p.batch_inner, b_in = bi - b_out * p.batch_inner;
+        b_out = bi / p.batch_inner;
+        b_in = bi - b_out * p.batch_inner;
         d_off = b_in * p.d_si + b_out * p.d_so;
         aux_off = b_in * p.aux_si + b_out * p.aux_so;
       }
@@ -796,6 +818,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         const int sub = lane >> 3, seg = lane & 7;
         et.row_base = row - lane;
         et.n0 = n0;
+        et.b_in = b_in;
+        et.b_out = b_out;
         et.interior = (et.row_base + 32 <= p.M) && (n0 + BN <= p.N);
         const long long elem0 = static_cast<long long>(et.row_base + sub) * p.ldd + n0 + seg * 8;
         et.out = reinterpret_cast<uint8_t*>(p.d) + (d_off + elem0) * 2;
@@ -850,6 +874,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           }
         }
         release_acc();
+      } else if (staged && p.tma_store) {
+        // st_in doubles as the second output buffer unless this epilogue needs it (aux staging / pre-activation copy)
+        const bool single = (et.aux != nullptr && p.act != 1) || (p.act == 1 && et.out2 != nullptr);
+#pragma unroll 1
+        for (int c2 = 0; c2 < num_groups; ++c2) {
+          uint8_t* ob = single ? st_out : st_out + (store_groups & 1) * 4096;
+          // the bulk store that last read this buffer (two groups ago, or the previous one in single mode) is done with it
+          if (lane == 0) {
+            if (single) tma_store_wait_read<0>(); else tma_store_wait_read<1>();
+          }
+          __syncwarp();
+          epilogue_group_compute(p, et, taddr + c2 * 64, c2, num_groups, ob, st_out + 4096, lane, areg);
+          if (c2 == num_groups - 1) release_acc();
+          epilogue_group_store_tma(p, et, c2, ob, st_out + 4096, lane);
+          ++store_groups;
+        }
       } else if (staged) {
 #pragma unroll 1
         for (int c2 = 0; c2 < num_groups; ++c2) {
@@ -870,6 +910,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (lane == 0) tma_store_wait_read<0>();     // shared memory must outlive the bulk stores that read it
+    __syncwarp();
   }
 
   tcgen05_fence_before();
@@ -1147,6 +1189,27 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
     // own rows first: start the n-block walk at the block holding this rank's first row
     p.g_rotate = static_cast<int>((static_cast<long long>(g->rank) * g->rows_per_rank / bn) % p.n_blocks);
     DTB_CUDA_OK(cudaMemsetAsync(g->flags, 0, sizeof(int) * (p.n_blocks + 1), static_cast<cudaStream_t>(stream)));
+  }
+
+  {
+    // TMA-store epilogue (DTB_GEMM_TMA_STORE=0: per-lane LDS + STG hand-off): same conditions as the staged epilogue
+    static const int tma_store = [] { const char* e = getenv("DTB_GEMM_TMA_STORE"); return (e && e[0] == '0') ? 0 : 1; }();
+    const bool staged = p.split_k == 1 && !p.direct_epilogue && !p.d_fp32 && !(p.aux != nullptr && p.aux_fp32) && (p.N & 7) == 0;
+    const bool strides_ok = (bi <= 1 || a->d_stride_inner % 8 == 0) && (bo <= 1 || a->d_stride_outer % 8 == 0);
+    p.tma_store = 0;
+    if (tma_store && staged && strides_ok) {
+      uint64_t dims[4] = {static_cast<uint64_t>(a->n), static_cast<uint64_t>(a->m), static_cast<uint64_t>(bi),
+                          static_cast<uint64_t>(bo)};
+      uint32_t box[4] = {64, 32, 1, 1};
+      const uint64_t row_bytes = static_cast<uint64_t>(a->ldd) * 2;
+      uint64_t strides[3];
+      strides[0] = row_bytes;
+      strides[1] = bi > 1 ? static_cast<uint64_t>(a->d_stride_inner) * 2 : row_bytes * dims[1];
+      strides[2] = bo > 1 ? static_cast<uint64_t>(a->d_stride_outer) * 2 : strides[1] * dims[2];
+      if (get_tensor_map_bf16(&p.map_d, a->d, dims, strides, box)) return 1;
+      if (a->d2 != nullptr && a->act == 1 && get_tensor_map_bf16(&p.map_d2, a->d2, dims, strides, box)) return 1;
+      p.tma_store = 1;
+    }
   }
 
   CUtensorMap ma, mb;
