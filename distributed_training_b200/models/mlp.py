@@ -74,9 +74,13 @@ class MLP(nn.Module):
             self._ws = {key: ws}      # one live batch shape at a time
         return ws
 
+    #: forward_backward accepts ``bwd_max_ctas`` (see ReplicatedModule: exclusive-mode reduction kernels)
+    supports_bwd_max_ctas = True
+
     def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, loss: str = "cross_entropy",
                          grad_sink: Any = None, max_ctas: int = 0,
-                         fused_sgd: Optional[Tuple[float, float]] = None, on_updated: Any = None) -> torch.Tensor:
+                         fused_sgd: Optional[Tuple[float, float]] = None, on_updated: Any = None,
+                         bwd_max_ctas: int = 0) -> torch.Tensor:
         """Fused training step (no autograd).  Returns the mean loss (0-dim fp32 tensor).
 
         ``grad_sink`` (a ``ReplicatedModule``) supplies ``grad_view(param)`` and
@@ -84,6 +88,8 @@ class MLP(nn.Module):
         ``fused_sgd=(lr, weight_decay)`` makes the wgrad GEMM epilogue apply the SGD update to the
         weight in place (single replica only); ``on_updated(params)`` is told which parameters were
         stepped that way so the optimizer skips them.
+        ``bwd_max_ctas`` caps the GEMM grids of backward once the first gradient has been handed to the reducer:
+        the data-parallel wrapper uses it to leave whole SMs to its exclusive-mode reduction kernels.
         """
         if loss != "cross_entropy" or targets.dtype != torch.int64:
             raise NotImplementedError("native MLP step supports cross_entropy with int64 class targets")
@@ -117,6 +123,7 @@ class MLP(nn.Module):
         native.mean_f32(ws["row_loss"], ws["loss"])
         # ---- backward, last layer first; each layer's grads go to the reducer as soon as queued
         dz = ws["logits"]
+        cap = max_ctas
         for i in range(n - 1, -1, -1):
             layer = self.layers[i]
             out_f, in_f = layer.weight.shape
@@ -127,13 +134,13 @@ class MLP(nn.Module):
                 # wgrad is handed to the reducer: a fused reduce+SGD (or the fused epilogue below) overwrites W_i.
                 nxt = ws["dz"][i % 2]
                 native.gemm(dz, layer.weight, nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
-                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=max_ctas)
+                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=cap)
             if fused_sgd is not None:
                 # single replica: W = (1 - lr*wd) W - lr * (dz^T h_in), applied in the wgrad epilogue (no dW in HBM)
                 lr, wd = fused_sgd
                 native.gemm(dz, h_in, layer.weight.data, m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
                             lda=dz.shape[1], ldb=in_f, aux=layer.weight.data, alpha=-lr, beta=1.0 - lr * wd,
-                            max_ctas=max_ctas)
+                            max_ctas=cap)
                 if on_updated is not None:
                     on_updated([layer.weight])
             elif i == 0 and getattr(grad_sink, "tail_chunks", lambda p: 1)(layer.weight) > 1:
@@ -143,18 +150,20 @@ class MLP(nn.Module):
                 gw, per = grad_of(layer.weight), out_f // nch
                 for c in range(nch):
                     native.gemm(dz[:, c * per:], h_in, gw[c * per:], m=per, n=in_f, k=rows, a_mn=True, b_mn=True,
-                                lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
+                                lda=dz.shape[1], ldb=in_f, max_ctas=cap)
                     grad_sink.mark_ready_chunk(layer.weight, c, nch)
             else:
                 # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major), straight into the gradient bucket
                 native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
-                            lda=dz.shape[1], ldb=in_f, max_ctas=max_ctas)
+                            lda=dz.shape[1], ldb=in_f, max_ctas=cap)
             if layer.bias is not None:
                 native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
             if grad_sink is not None:
                 grad_sink.mark_ready(layer.weight)
                 if layer.bias is not None:
                     grad_sink.mark_ready(layer.bias)
+                if bwd_max_ctas:
+                    cap = bwd_max_ctas
             if nxt is not None:
                 dz = nxt
         return ws["loss"]

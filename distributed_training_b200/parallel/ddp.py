@@ -298,10 +298,21 @@ class ReplicatedModule(nn.Module):
                 # single replica: the wgrad GEMM epilogue applies W -= lr*(dW + wd*W) itself
                 kwargs["fused_sgd"] = hyper
                 kwargs["on_updated"] = self._optimizer.mark_updated
+            # exclusive-mode reduction: backward GEMMs leave `exclusive_sms` SMs free and the large all-reduces run
+            # there on whole-SM CTAs at their stand-alone speed instead of fighting a GEMM CTA for its SM
+            excl = int(getattr(self.comm, "exclusive_sms", 0) or 0)
+            use_excl = (excl > 0 and self.comm.world_size > 1 and self.comm.device.type == "cuda"
+                        and getattr(self.module, "supports_bwd_max_ctas", False))
+            if use_excl:
+                sms = torch.cuda.get_device_properties(self.comm.device).multi_processor_count
+                kwargs.setdefault("bwd_max_ctas", max(2, (sms - excl) & ~1))
+                self.comm.exclusive_now = True
             loss = self.module.forward_backward(inputs, targets, grad_sink=self, **kwargs)
             self.finish_gradient_sync()
         finally:
             self._in_manual_step = False
+            if hasattr(self.comm, "exclusive_now"):
+                self.comm.exclusive_now = False
         return loss
 
     def finish_gradient_sync(self) -> None:

@@ -95,6 +95,7 @@ class SymmComm(Communicator):
         #: the GEMM's dynamic tile scheduler works around the SMs they hold.  DTB_COMM_EXCLUSIVE_SMS overrides.
         self.exclusive_sms = int(os.environ.get("DTB_COMM_EXCLUSIVE_SMS", "0"))
         self.exclusive_min_bytes = 8 << 20
+        self.exclusive_now = False     # set by the data-parallel wrapper while a step that left SMs free is running
         #: opt-in (DTB_COMM_CE=1): large bf16 all-reduces move their NVLink legs with the copy engines
         #: (dtb_comm_all_reduce_ce).  Local DMA traffic barely slows a GEMM, but measured at 2 GPUs the peer copies ran
         #: at ~1/3 of their solo rate beside the GEMMs and the step was 0.4 ms slower than with co-resident comm CTAs
@@ -225,7 +226,7 @@ class SymmComm(Communicator):
         torch.cuda.current_stream().synchronize()
 
     def _ctas_for(self, nbytes: int) -> int:
-        if self.exclusive_sms > 0 and nbytes >= self.exclusive_min_bytes:
+        if self.exclusive_sms > 0 and self.exclusive_now and nbytes >= self.exclusive_min_bytes:
             return self.exclusive_sms | native.EXCLUSIVE
         return self.comm_ctas
 
