@@ -77,6 +77,35 @@ def collectives(rank, world, port, out_dir):
                 got = _gather_cpu(par, world)
                 assert all(torch.equal(got[0], t) for t in got), "ranks disagree bitwise after ce sgd"
         comm.copy_engine_min_bytes = 16 << 20
+        comm.copy_engine = False
+        # ---- exclusive mode (whole-SM 1024-thread CTAs in clusters of two: what large DDP buckets take while backward
+        # GEMMs leave SMs free): same bitwise contract as the co-resident kernels ----
+        comm.exclusive_sms, comm.exclusive_now, comm.exclusive_min_bytes = 4, True, 1 << 16
+        for n in (world * 16 * 4096, world * 16 * 100_000 + 16 * 8):
+            comm.reserve(2 * n * 2 + 4096)
+            buf, par = comm.alloc(n, torch.bfloat16), comm.alloc(n, torch.bfloat16)
+            assert comm._ctas_for(n * 2) & (1 << 20)
+            for rep in range(2):
+                g = torch.Generator().manual_seed(91 * rep + n)
+                per_rank = [torch.randn(n, generator=g).to(torch.bfloat16) for _ in range(world)]
+                p0 = torch.randn(n, generator=g).to(torch.bfloat16)
+                acc = torch.zeros(n)
+                for r in range(world):
+                    acc += per_rank[r].float()
+                mean = acc / world
+                buf.copy_(per_rank[rank])
+                comm.all_reduce_avg_(buf).wait()
+                torch.cuda.synchronize()
+                assert torch.equal(buf.cpu(), mean.to(torch.bfloat16)), ("exclusive mean", n, rep)
+                buf.copy_(per_rank[rank])
+                par.copy_(p0)
+                comm.all_reduce_sgd_(buf, par, 0.05, 0.01).wait()
+                torch.cuda.synchronize()
+                expect = p0.float() * (1 - 0.05 * 0.01) - 0.05 * mean
+                assert torch.allclose(par.cpu().float(), expect, rtol=2 ** -7, atol=1e-6), ("exclusive sgd", n, rep)
+                got = _gather_cpu(par, world)
+                assert all(torch.equal(got[0], t) for t in got), "ranks disagree bitwise after exclusive sgd"
+        comm.exclusive_now = False
         # ---- broadcast ----
         t1 = torch.full((1000, 33), float(rank + 1), device=dev)
         t2 = torch.full((7,), float(rank + 5), device=dev, dtype=torch.bfloat16)
