@@ -60,3 +60,29 @@ def test_gpt2_under_replicated_and_sharded_wrappers():
     for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
         assert torch.allclose(p.grad, q.grad, atol=1e-5), n
     assert list(sb.state_dict().keys()) == list(a.state_dict().keys())
+
+
+def test_step_params_equals_whole_model_step():
+    """Stepping parameters bucket by bucket (what the data-parallel wrapper does behind each all-reduce) must give
+    bit-identical results to one step() over the whole model, for both fused optimizers."""
+    import torch
+    from distributed_training_b200.optim import FusedAdamW, FusedSGD
+
+    def run(split, cls, **kw):
+        torch.manual_seed(0)
+        ps = [torch.nn.Parameter(torch.randn(5, 3)) for _ in range(4)]
+        opt = cls(ps, lr=1e-2, **kw)
+        for _ in range(3):
+            for p in ps:
+                p.grad = torch.randn_like(p)
+            if split:
+                opt.step_params(ps[:2])
+                opt.step_params(ps[1:3])        # overlapping call: already-updated parameters are skipped
+                assert [len(opt._pending(g)) for g in opt.param_groups] == [1]
+            opt.step()
+            assert not opt._already_updated
+        return [p.detach().clone() for p in ps]
+
+    for cls, kw in ((FusedAdamW, dict(master_weights=False)), (FusedSGD, dict(momentum=0.9, weight_decay=0.1))):
+        a, b = run(False, cls, **kw), run(True, cls, **kw)
+        assert all(torch.equal(x, y) for x, y in zip(a, b)), cls.__name__
