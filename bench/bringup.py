@@ -10,8 +10,6 @@ from __future__ import annotations
 import argparse
 import itertools
 import json
-import math
-import os
 import subprocess
 import sys
 import time

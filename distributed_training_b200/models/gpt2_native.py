@@ -21,7 +21,7 @@ The reference has no transformer; the baseline for this path is eag
 """
 from __future__ import annotations
 
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict
 
 import torch
 from torch import nn

@@ -12,7 +12,6 @@ handed to the reducer the moment a layer's wgrad has been queued.
 """
 from __future__ import annotations
 
-import math
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch

@@ -10,7 +10,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 from pathlib import Path
-from typing import List, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 

@@ -30,7 +30,7 @@ from __future__ import annotations
 import logging
 import math
 from collections import OrderedDict
-from typing import Any, Dict, Iterable, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Tuple
 
 import torch
 from torch import nn

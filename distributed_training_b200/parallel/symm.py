@@ -18,7 +18,6 @@ sizes in the same order (true for replicas of one model).
 """
 from __future__ import annotations
 
-import ctypes as C
 import logging
 import os
 from dataclasses import dataclass

@@ -26,13 +26,12 @@ import logging
 import os
 import sys
 import time
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from pathlib import Path
 from typing import Any, Callable, Optional, Tuple, Union
 
 import torch
 import torch.distributed as dist
-import torch.nn.functional as F
 
 from . import hydra_compat
 from .data import (LinearTeacherDataset, MyTrainDataset, ShardedLoader, ShardedSampler, TokenDataset,

@@ -1,7 +1,6 @@
 """Per-rank bodies for the multi-process (gloo) tests; must be importable by spawned children."""
 import os
 import sys
-import types
 from pathlib import Path
 
 import torch

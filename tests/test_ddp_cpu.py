@@ -1,6 +1,4 @@
 """Distributed plumbing on CPU/gloo, world 2 and 4 (SURVEY §4.3 tier 2; BASELINE.json config 1)."""
-import os
-
 import pytest
 import torch
 import torch.multiprocessing as mp
