@@ -103,8 +103,10 @@ def _ok(rc: int) -> None:
         raise RuntimeError(f"dtb200: {lib().dtb_last_error().decode()} (rc={rc})")
 
 
-def _stream() -> C.c_void_p:
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+def _stream(handle: Optional[int] = None) -> C.c_void_p:
+    """The stream a launch goes to: torch's current stream, or an explicit raw handle (callers that launch on a side
+    stream pass it directly -- entering a ``torch.cuda.stream`` context costs ~10 us of host time per launch)."""
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream if handle is None else handle)
 
 
 def _p(t: Optional[torch.Tensor]) -> C.c_void_p:
@@ -193,7 +195,7 @@ def gemm_allgather(a: torch.Tensor, b_full: torch.Tensor, out: torch.Tensor, pee
                    flags: torch.Tensor, rank: int, rows_per_rank: int, *, m: int, n: int, k: int,
                    bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None, act: int = 0,
                    d2: Optional[torch.Tensor] = None, beta: float = 1.0, max_ctas: int = 0, tile_n: int = 0,
-                   cta_pair: int = 0) -> torch.Tensor:
+                   cta_pair: int = 0, gather_args: Optional["GatherArgs"] = None) -> torch.Tensor:
     """Linear forward whose weight all-gather runs inside the GEMM kernel (``dtb_gemm_bf16_allgather``).
 
     ``b_full`` is the local [n, k] weight buffer that receives the gathered rows; ``peer_shard_ptrs[r]`` is
@@ -212,13 +214,19 @@ def gemm_allgather(a: torch.Tensor, b_full: torch.Tensor, out: torch.Tensor, pee
     args.act = act
     args.alpha, args.beta = 1.0, beta
     args.tile_n, args.cta_pair, args.max_ctas = tile_n, cta_pair, max_ctas
+    g = gather_args if gather_args is not None else make_gather_args(peer_shard_ptrs, flags, rank, rows_per_rank)
+    _ok(lib().dtb_gemm_bf16_allgather(C.byref(args), C.byref(g), _stream()))
+    return out
+
+
+def make_gather_args(peer_shard_ptrs: Sequence[int], flags: torch.Tensor, rank: int, rows_per_rank: int) -> "GatherArgs":
+    """The per-weight constant half of a ``gemm_allgather`` call (build once, pass as ``gather_args``)."""
     g = GatherArgs()
     for r, ptr in enumerate(peer_shard_ptrs):
         g.peer_shard[r] = ptr
     g.flags = flags.data_ptr()
     g.world, g.rank, g.rows_per_rank = len(peer_shard_ptrs), rank, rows_per_rank
-    _ok(lib().dtb_gemm_bf16_allgather(C.byref(args), C.byref(g), _stream()))
-    return out
+    return g
 
 
 def linear_small_fwd(x, w, b, y):
@@ -445,57 +453,57 @@ def _cta_arg(max_ctas: int, channel: int) -> int:
     return (max_ctas & 0xFFFF) | ((channel & 0xF) << 16) | (max_ctas & EXCLUSIVE)
 
 
-def comm_barrier(desc: CommDesc, channel: int = 0):
-    _ok(lib().dtb_comm_barrier(C.byref(desc), channel, _stream()))
+def comm_barrier(desc: CommDesc, channel: int = 0, stream: Optional[int] = None):
+    _ok(lib().dtb_comm_barrier(C.byref(desc), channel, _stream(stream)))
 
 
-def comm_broadcast(desc: CommDesc, offset: int, nbytes: int, root: int, max_ctas: int = 0, channel: int = 0):
+def comm_broadcast(desc: CommDesc, offset: int, nbytes: int, root: int, max_ctas: int = 0, channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_broadcast(C.byref(desc), C.c_size_t(offset), C.c_size_t(nbytes), root,
-                                 _cta_arg(max_ctas, channel), _stream()))
+                                 _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def comm_all_reduce_avg(desc: CommDesc, offset: int, numel: int, fp32: bool, algo: int = 0, max_ctas: int = 0,
-                        channel: int = 0):
+                        channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_all_reduce_avg(C.byref(desc), C.c_size_t(offset), C.c_longlong(numel), int(fp32), algo,
-                                      _cta_arg(max_ctas, channel), _stream()))
+                                      _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def comm_all_reduce_sgd(desc: CommDesc, grad_offset: int, param_offset: int, numel: int, lr: float,
-                        weight_decay: float, max_ctas: int = 0, channel: int = 0):
+                        weight_decay: float, max_ctas: int = 0, channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_all_reduce_sgd(C.byref(desc), C.c_size_t(grad_offset), C.c_size_t(param_offset),
                                       C.c_longlong(numel), C.c_float(lr), C.c_float(weight_decay),
-                                      _cta_arg(max_ctas, channel), _stream()))
+                                      _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def comm_all_reduce_ce(desc: CommDesc, grad_offset: int, param_offset: int, sgd: bool, numel: int,
                        staging: torch.Tensor, lr: float = 0.0, weight_decay: float = 0.0, max_ctas: int = 0,
-                       channel: int = 0):
+                       channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_all_reduce_ce(C.byref(desc), C.c_size_t(grad_offset), C.c_size_t(param_offset), int(sgd),
                                      C.c_longlong(numel), _p(staging),
                                      C.c_size_t(staging.numel() * staging.element_size()), C.c_float(lr),
-                                     C.c_float(weight_decay), _cta_arg(max_ctas, channel), _stream()))
+                                     C.c_float(weight_decay), _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def comm_all_gather(desc: CommDesc, dst_offset: int, src_offset: int, numel: int, esize: int, max_ctas: int = 0,
-                    channel: int = 0):
+                    channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_all_gather(C.byref(desc), C.c_size_t(dst_offset), C.c_size_t(src_offset), C.c_longlong(numel),
-                                  esize, _cta_arg(max_ctas, channel), _stream()))
+                                  esize, _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def comm_reduce_scatter_avg(desc: CommDesc, out: torch.Tensor, src_offset: int, numel: int, src_fp32: bool,
-                            max_ctas: int = 0, channel: int = 0):
+                            max_ctas: int = 0, channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_reduce_scatter_avg(C.byref(desc), _p(out), int(out.dtype == torch.float32),
                                           C.c_size_t(src_offset), C.c_longlong(numel), int(src_fp32),
-                                          _cta_arg(max_ctas, channel), _stream()))
+                                          _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def comm_rs_optim(desc: CommDesc, grad_offset: int, shard_offset: int, master, m, v, numel: int, opt: int,
                   lr: float, b1: float, b2: float, eps: float, wd: float, bc1: float, bc2: float, momentum: float,
-                  max_ctas: int = 0, channel: int = 0):
+                  max_ctas: int = 0, channel: int = 0, stream: Optional[int] = None):
     _ok(lib().dtb_comm_rs_optim(C.byref(desc), C.c_size_t(grad_offset), C.c_size_t(shard_offset), _p(master), _p(m),
                                 _p(v), C.c_longlong(numel), opt, C.c_float(lr), C.c_float(b1), C.c_float(b2),
                                 C.c_float(eps), C.c_float(wd), C.c_float(bc1), C.c_float(bc2), C.c_float(momentum),
-                                _cta_arg(max_ctas, channel), _stream()))
+                                _cta_arg(max_ctas, channel), _stream(stream)))
 
 
 def debug_stream_probe(a, b, p, q, nbytes: int, ctas: int):
