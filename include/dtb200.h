@@ -213,7 +213,9 @@ int dtb_comm_barrier(const dtb_comm* c, int channel, void* stream);
 /* buf[offset .. +bytes) on every rank = root's */
 int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes, int root, int max_ctas, void* stream);
 /* in-place mean over ranks of n elements at `offset` (dtype: 0 bf16, 1 fp32); algo: 0 auto, 1 one-shot,
- * 2 two-shot, 3 NVLS multimem */
+ * 2 two-shot.  3 is reserved for an NVLS (multimem) variant and is rejected with an error in this build: the
+ * symmetric heap is cudaMalloc + CUDA IPC, which cannot be bound to a multicast object.  OR 1<<20 into max_ctas to
+ * run a large bf16 two-shot reduction on whole-SM 1024-thread CTAs (the caller must have left that many SMs free). */
 int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long long n, int dtype, int algo, int max_ctas,
                             void* stream);
 /* Gradient all-reduce fused with the optimizer step (bf16): rank r averages slice r of the gradients over
