@@ -4,6 +4,9 @@ The wrappers take torch tensors, pass raw device pointers plus the *current*
 CUDA stream, and never fall back to PyTorch: if the library is missing on a
 machine that has a GPU, :func:`lib` raises, so a silent eager fallback cannot
 masquerade as the native path.
+
+The reference has no native layer of its own; these entry points stand in for the torch internals it executes
+(DDP init broadcast and Reducer, c10d collectives, ATen/cuBLAS GEMMs, loss and optimizer kernels).
 """
 from __future__ import annotations
 
