@@ -7,7 +7,14 @@
 // (st.release.sys) into d's pad at [c][b][s]; d spins with ld.acquire.sys.
 // Sequence numbers only grow (the next value is kept in the pad as well), so
 // flags are never reset and back-to-back launches cannot confuse each other.
-// A bounded spin turns a dead peer into an error flag instead of a GPU hang.
+// A bounded spin turns a dead peer into an error flag instead of a GPU hang: the CTA that timed out records the
+// missing peer in ERR_SLOT and the whole CTA leaves the kernel WITHOUT touching the payload; every later collective on
+// that communicator sees the flag at entry and returns at once, and the host (Trainer) raises at its next check.
+//
+// NVLS: when the heap is VMM-backed and bound to a multicast object (symm.cu), `mc_base` is the multicast mapping of
+// the same bytes.  multimem.ld_reduce on it returns the sum over all ranks computed inside the NVSwitch (fp32
+// accumulation), multimem.st writes all ranks' copies with one store.  The *_nvls kernels use those instead of W peer
+// loads + W peer stores per vector; the flag barriers stay on unicast peer addresses.
 //
 //   all-reduce (two-shot)   rank r reduces slice r from all peers in fixed rank
 //                           order (fp32), scales by 1/W, casts, and stores the
@@ -56,7 +63,9 @@ __device__ __forceinline__ int flag_slot(int channel, int block, int src_rank) {
 // Block-level barrier across ranks.  All threads of the block call it; on return
 // every peer's block with the same index has arrived and its earlier stores are
 // visible here.  `seq` is this block's running sequence number (register copy).
-__device__ __forceinline__ void rank_barrier(const Ctx& x, uint32_t& seq) {
+__device__ __forceinline__ bool rank_barrier(const Ctx& x, uint32_t& seq) {
+  __shared__ int s_dead;
+  if (threadIdx.x == 0) s_dead = 0;
   __syncthreads();
   seq += 1;
   if (threadIdx.x < static_cast<unsigned>(x.c.world)) {
@@ -68,11 +77,19 @@ __device__ __forceinline__ void rank_barrier(const Ctx& x, uint32_t& seq) {
     while (static_cast<int32_t>(ld_acquire_sys(mine) - seq) < 0) {
       if (clock64() - t0 > limit) {
         x.c.signals[x.c.rank][ERR_SLOT] = 1u + static_cast<uint32_t>(peer);
+        __threadfence_system();
+        s_dead = 1;
         break;
       }
     }
   }
   __syncthreads();
+  return s_dead == 0;
+}
+
+// True when an earlier collective on this communicator already timed out: nothing may touch the payload any more.
+__device__ __forceinline__ bool comm_dead(const Ctx& x) {
+  return *reinterpret_cast<const volatile uint32_t*>(x.c.signals[x.c.rank] + ERR_SLOT) != 0u;
 }
 
 __device__ __forceinline__ uint32_t load_seq(const Ctx& x) {
@@ -136,8 +153,9 @@ __device__ __forceinline__ void reduce_vec(const Ctx& x, size_t byte_off, float*
 
 // ---- kernels ------------------------------------------------------------------
 __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) barrier_kernel(const Ctx x) {
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   store_seq(x, seq);
 }
 
@@ -163,8 +181,9 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
 allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec, const SgdArgs sgd) {
   constexpr int U = Unroll<W>::U;
   constexpr int N = Vec<FP32>::N;
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);   // every rank's gradients are final (and, for SGD, nobody still reads the old params)
+  if (!rank_barrier(x, seq)) return;   // every rank's gradients are final (and, for SGD, nobody still reads the old params)
   const long long lo = nvec * x.c.rank / W, hi = nvec * (x.c.rank + 1) / W;
   const float scale = 1.f / W;
   const long long stride = static_cast<long long>(gridDim.x) * THREADS;
@@ -210,7 +229,7 @@ allreduce_twoshot_kernel(const Ctx x, size_t offset, long long nvec, const SgdAr
       for (int r = 0; r < W; ++r) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + dst, out);
     }
   }
-  rank_barrier(x, seq);   // every slice has been delivered to this rank
+  if (!rank_barrier(x, seq)) return;   // every slice has been delivered to this rank
   store_seq(x, seq);
 }
 
@@ -246,8 +265,9 @@ __global__ void __launch_bounds__(NT, NT == THREADS ? MIN_CTAS_PER_SM : 1)
 allreduce_twoshot256_kernel(const Ctx x, size_t offset, long long nvec32, const SgdArgs sgd) {
   constexpr int G = W < 4 ? W : 4;          // loads in flight per batch
   constexpr int U = W <= 2 ? 2 : 1;
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   const long long lo = nvec32 * x.c.rank / W, hi = nvec32 * (x.c.rank + 1) / W;
   const float scale = 1.f / W;
   const long long stride = static_cast<long long>(gridDim.x) * NT;
@@ -299,7 +319,7 @@ allreduce_twoshot256_kernel(const Ctx x, size_t offset, long long nvec32, const 
       for (int r = 0; r < W; ++r) st256_stream(static_cast<uint8_t*>(x.c.peers[r]) + dst, out);
     }
   }
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   store_seq(x, seq);
 }
 
@@ -307,8 +327,9 @@ allreduce_twoshot256_kernel(const Ctx x, size_t offset, long long nvec32, const 
 // registers, all ranks meet (nobody may overwrite data a peer still reads), then store.
 template <bool FP32, int W, int PER_THREAD>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allreduce_oneshot_kernel(const Ctx x, size_t offset, long long nvec) {
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   float acc[PER_THREAD][Vec<FP32>::N];
   const long long base = static_cast<long long>(blockIdx.x) * THREADS * PER_THREAD + threadIdx.x;
   const float scale = 1.f / W;
@@ -317,7 +338,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allreduce_oneshot_ke
     const long long v = base + static_cast<long long>(i) * THREADS;
     if (v < nvec) reduce_vec<FP32, W>(x, offset + static_cast<size_t>(v) * 16, acc[i]);
   }
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
 #pragma unroll
   for (int i = 0; i < PER_THREAD; ++i) {
     const long long v = base + static_cast<long long>(i) * THREADS;
@@ -331,8 +352,9 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allreduce_oneshot_ke
 }
 
 __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) broadcast_kernel(const Ctx x, size_t offset, long long nvec, int root) {
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);   // destinations are free to be overwritten
+  if (!rank_barrier(x, seq)) return;   // destinations are free to be overwritten
   if (x.c.rank == root) {
     const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[root]) + offset;
     for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec;
@@ -342,14 +364,15 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) broadcast_kernel(con
         if (r != root) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + offset + v * 16, val);
     }
   }
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   store_seq(x, seq);
 }
 
 // Push all-gather: rank r stores its shard (nvec vectors at src_off) to dst_off + r*shard on every rank.
 __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allgather_kernel(const Ctx x, size_t dst_off, size_t src_off, long long nvec) {
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[x.c.rank]) + src_off;
   const size_t slot = dst_off + static_cast<size_t>(x.c.rank) * static_cast<size_t>(nvec) * 16;
   for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec;
@@ -357,7 +380,140 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM) allgather_kernel(con
     const uint4 val = *reinterpret_cast<const uint4*>(src + v * 16);
     for (int r = 0; r < x.c.world; ++r) st_v4(static_cast<uint8_t*>(x.c.peers[r]) + slot + v * 16, val);
   }
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
+  store_seq(x, seq);
+}
+
+
+// ---- NVLS (multimem) variants ---------------------------------------------------------------------------------------
+// `mc` addresses are offsets into dtb_comm::mc_base, the multicast mapping of the symmetric segment.
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ uint4 mm_ld_reduce_f32(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+template <bool FP32>
+__device__ __forceinline__ uint4 mm_ld_reduce(const void* mc) {
+  return FP32 ? mm_ld_reduce_f32(mc) : mm_ld_reduce_bf16(mc);
+}
+__device__ __forceinline__ void mm_st(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
+// Two-shot mean (optionally fused with SGD) through the switch: rank r asks the NVSwitch for the sum of slice r over
+// all ranks (one multimem.ld_reduce per 16 bytes instead of W peer loads), scales / applies the update, and writes the
+// result into every rank with one multimem.st (instead of W peer stores).  Per GPU and direction that is (1 + 1/W) x
+// the buffer over NVLink instead of 2 (W-1)/W x, and 2 memory instructions per vector instead of 2 W, so far fewer
+// SM cycles are taken from the GEMMs that run beside it.  The sum is formed in fp32 inside the switch in an order the
+// hardware chooses: all ranks receive the SAME value (one reduction, broadcast), but it may differ in the last bit
+// from the fixed-rank-order sum of the peer-load kernels.
+// NT = 256: co-resident CTAs; NT = 1024: exclusive whole-SM CTAs (see allreduce_twoshot256_kernel).
+template <bool FP32, bool SGD, int NT>
+__global__ void __launch_bounds__(NT, NT == THREADS ? MIN_CTAS_PER_SM : 1)
+allreduce_nvls_kernel(const Ctx x, size_t offset, long long nvec, const SgdArgs sgd) {
+  constexpr int U = 4;
+  constexpr int N = Vec<FP32>::N;
+  if (comm_dead(x)) return;
+  uint32_t seq = load_seq(x);
+  if (!rank_barrier(x, seq)) return;
+  const int W = x.c.world;
+  const long long lo = nvec * x.c.rank / W, hi = nvec * (x.c.rank + 1) / W;
+  const float scale = 1.f / static_cast<float>(W);
+  uint8_t* mc = static_cast<uint8_t*>(x.c.mc_base);
+  const uint8_t* mine = static_cast<const uint8_t*>(x.c.peers[x.c.rank]);
+  const long long stride = static_cast<long long>(gridDim.x) * NT;
+  for (long long v0 = lo + static_cast<long long>(blockIdx.x) * NT + threadIdx.x; v0 < hi; v0 += stride * U) {
+    uint4 raw[U];
+    uint4 praw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long v = v0 + u * stride;
+      if (v < hi) {
+        raw[u] = mm_ld_reduce<FP32>(mc + offset + static_cast<size_t>(v) * 16);
+        if (SGD) praw[u] = *reinterpret_cast<const uint4*>(mine + sgd.param_offset + static_cast<size_t>(v) * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= hi) break;
+      float acc[N];
+      Vec<FP32>::unpack(raw[u], acc);
+      size_t dst = offset + static_cast<size_t>(v) * 16;
+      if (SGD) {
+        dst = sgd.param_offset + static_cast<size_t>(v) * 16;
+        float pf[N];
+        Vec<FP32>::unpack(praw[u], pf);
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] = pf[j] * sgd.decay - sgd.lr * (acc[j] * scale);
+      } else {
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[j] *= scale;
+      }
+      mm_st(mc + dst, Vec<FP32>::pack(acc));
+    }
+  }
+  if (!rank_barrier(x, seq)) return;
+  store_seq(x, seq);
+}
+
+// Broadcast: the root writes every rank's copy (its own included) with one multimem.st per vector: the root's link
+// carries the buffer once instead of W-1 times.
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
+broadcast_nvls_kernel(const Ctx x, size_t offset, long long nvec, int root) {
+  if (comm_dead(x)) return;
+  uint32_t seq = load_seq(x);
+  if (!rank_barrier(x, seq)) return;
+  if (x.c.rank == root) {
+    const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[root]) + offset;
+    uint8_t* mc = static_cast<uint8_t*>(x.c.mc_base) + offset;
+    const long long stride = static_cast<long long>(gridDim.x) * THREADS;
+    for (long long v0 = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v0 < nvec; v0 += stride * 4) {
+      uint4 val[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (v0 + u * stride < nvec) val[u] = *reinterpret_cast<const uint4*>(src + (v0 + u * stride) * 16);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (v0 + u * stride < nvec) mm_st(mc + (v0 + u * stride) * 16, val[u]);
+    }
+  }
+  if (!rank_barrier(x, seq)) return;
+  store_seq(x, seq);
+}
+
+// All-gather: rank r writes its shard into slot r of every rank with one multimem.st per vector.
+__global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
+allgather_nvls_kernel(const Ctx x, size_t dst_off, size_t src_off, long long nvec) {
+  if (comm_dead(x)) return;
+  uint32_t seq = load_seq(x);
+  if (!rank_barrier(x, seq)) return;
+  const uint8_t* src = static_cast<const uint8_t*>(x.c.peers[x.c.rank]) + src_off;
+  uint8_t* mc = static_cast<uint8_t*>(x.c.mc_base) + dst_off + static_cast<size_t>(x.c.rank) * static_cast<size_t>(nvec) * 16;
+  const long long stride = static_cast<long long>(gridDim.x) * THREADS;
+  for (long long v0 = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v0 < nvec; v0 += stride * 4) {
+    uint4 val[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v0 + u * stride < nvec) val[u] = *reinterpret_cast<const uint4*>(src + (v0 + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v0 + u * stride < nvec) mm_st(mc + (v0 + u * stride) * 16, val[u]);
+  }
+  if (!rank_barrier(x, seq)) return;
   store_seq(x, seq);
 }
 
@@ -369,18 +525,25 @@ struct OptArgs {
 };
 
 // Reduce-scatter (mean) of slice `rank`; MODE 0: write fp32/bf16 result to `out`; MODE 1: fused optimizer.
-template <bool FP32, int W, int MODE>
+// NVLS = true: the W peer loads of a vector become one multimem.ld_reduce on the multicast mapping (summed in the
+// switch, W then only sets the 1/W scale).
+template <bool FP32, int W, int MODE, bool NVLS = false>
 __global__ void __launch_bounds__(THREADS, MIN_CTAS_PER_SM)
 reduce_scatter_kernel(const Ctx x, size_t src_off, long long nvec, void* out, int out_fp32, const OptArgs o) {
+  if (comm_dead(x)) return;
   uint32_t seq = load_seq(x);
-  rank_barrier(x, seq);
+  if (!rank_barrier(x, seq)) return;
   const size_t slice = src_off + static_cast<size_t>(x.c.rank) * static_cast<size_t>(nvec) * 16;
   const float scale = 1.f / W;
   constexpr int N = Vec<FP32>::N;
   for (long long v = static_cast<long long>(blockIdx.x) * THREADS + threadIdx.x; v < nvec;
        v += static_cast<long long>(gridDim.x) * THREADS) {
     float g[N];
-    reduce_vec<FP32, W>(x, slice + static_cast<size_t>(v) * 16, g);
+    if (NVLS) {
+      Vec<FP32>::unpack(mm_ld_reduce<FP32>(static_cast<const uint8_t*>(x.c.mc_base) + slice + static_cast<size_t>(v) * 16), g);
+    } else {
+      reduce_vec<FP32, W>(x, slice + static_cast<size_t>(v) * 16, g);
+    }
 #pragma unroll
     for (int j = 0; j < N; ++j) g[j] *= scale;
     const long long e = v * N;
@@ -430,7 +593,7 @@ reduce_scatter_kernel(const Ctx x, size_t src_off, long long nvec, void* out, in
         *reinterpret_cast<__nv_bfloat162*>(o.shard + e + j) = __floats2bfloat162_rn(w[j], w[j + 1]);
     }
   }
-  rank_barrier(x, seq);   // peers may reuse their gradient buffers only after every owner has read them
+  if (!rank_barrier(x, seq)) return;   // peers may reuse their gradient buffers only after every owner has read them
   store_seq(x, seq);
 }
 
@@ -447,6 +610,15 @@ static int pick_grid(long long nvec, int max_ctas, int dflt) {
 static bool wide_enabled() {
   static const bool on = [] { const char* e = getenv("DTB_COMM_WIDE"); return !(e && e[0] == '0'); }();
   return on;
+}
+
+// DTB_COMM_NVLS: unset = the multimem kernels carry the bandwidth-bound collectives when the heap has a multicast
+// mapping and world >= 4 (with 2 ranks the switch path moves 1.5x the buffer per direction, peer loads only 1x);
+// 0 = never; 1 = whenever a multicast mapping exists (also at world 2).
+static bool use_nvls(const dtb_comm* c) {
+  static const int mode = [] { const char* e = getenv("DTB_COMM_NVLS"); return e ? atoi(e) : -1; }();
+  if (c->mc_base == nullptr || c->world < 2 || mode == 0) return false;
+  return mode == 1 || c->world >= 4;
 }
 
 static int check(const dtb_comm* c, int channel) {
@@ -498,6 +670,26 @@ static cudaError_t launch_exclusive(const Ctx& x, size_t offset, long long nvec3
   return cudaLaunchKernelEx(&cfg, allreduce_twoshot256_kernel<W, SGD, EXCLUSIVE_THREADS>, x, offset, nvec32, sgd);
 }
 
+template <bool FP32, bool SGD>
+static cudaError_t launch_exclusive_nvls(const Ctx& x, size_t offset, long long nvec, const SgdArgs& sgd, int ctas,
+                                         cudaStream_t s) {
+  if (ctas < 2) ctas = 2;
+  if (ctas > MAX_BLOCKS) ctas = MAX_BLOCKS;
+  ctas &= ~1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(ctas));
+  cfg.blockDim = dim3(EXCLUSIVE_THREADS);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, allreduce_nvls_kernel<FP32, SGD, EXCLUSIVE_THREADS>, x, offset, nvec, sgd);
+}
+
 extern "C" int dtb_comm_barrier(const dtb_comm* c, int channel, void* stream) {
   if (check(c, channel)) return 2;
   Ctx x = {*c, channel};
@@ -513,8 +705,9 @@ extern "C" int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes
   if (bytes == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = static_cast<long long>(bytes / 16);
-  broadcast_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 64), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, offset, nvec,
-                                                                                                        root);
+  const int grid = pick_grid(nvec, ctas_of(max_ctas), 64);
+  if (use_nvls(c)) broadcast_nvls_kernel<<<grid, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, offset, nvec, root);
+  else broadcast_kernel<<<grid, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, offset, nvec, root);
   DTB_LAUNCH_OK();
   return 0;
 }
@@ -524,15 +717,27 @@ extern "C" int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long lo
   if (check(c, channel_of(max_ctas))) return 2;
   const int esize = dtype == 1 ? 4 : 2;
   DTB_REQUIRE(offset % 16 == 0 && (n * esize) % 16 == 0, "dtb_comm_all_reduce_avg: buffer must be 16-byte granular");
-  DTB_REQUIRE(algo != 3, "dtb_comm_all_reduce_avg: NVLS multimem path is not mapped in this build");
+  DTB_REQUIRE(algo != 3 || (c->mc_base != nullptr && c->world >= 2),
+              "dtb_comm_all_reduce_avg: algo 3 (NVLS) needs a multicast mapping of the heap (dtb_comm.mc_base) and >= 2 ranks");
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * esize / 16;
   auto s = static_cast<cudaStream_t>(stream);
   constexpr int PT = 4;
   const long long oneshot_cap = 64LL * 1024 / 16;   // <= 64 KiB
-  if (algo == 0) algo = (nvec <= oneshot_cap) ? 1 : 2;
-  if (algo == 1) {
+  if (algo == 0) algo = (nvec <= oneshot_cap) ? 1 : (use_nvls(c) ? 3 : 2);
+  if (algo == 3) {
+    const int grid = pick_grid(nvec / c->world / 4 + 1, ctas_of(max_ctas), 64);
+    const SgdArgs none = {0, 0.f, 1.f};
+    if (exclusive_of(max_ctas)) {
+      if (dtype == 1) DTB_CUDA_OK((launch_exclusive_nvls<true, false>(x, offset, nvec, none, ctas_of(max_ctas), s)));
+      else DTB_CUDA_OK((launch_exclusive_nvls<false, false>(x, offset, nvec, none, ctas_of(max_ctas), s)));
+    } else if (dtype == 1) {
+      allreduce_nvls_kernel<true, false, THREADS><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
+    } else {
+      allreduce_nvls_kernel<false, false, THREADS><<<grid, THREADS, 0, s>>>(x, offset, nvec, none);
+    }
+  } else if (algo == 1) {
     const long long per_block = static_cast<long long>(THREADS) * PT;
     const long long blocks = (nvec + per_block - 1) / per_block;
     DTB_REQUIRE(blocks <= MAX_BLOCKS, "dtb_comm_all_reduce_avg: one-shot limited to %lld bytes",
@@ -568,6 +773,12 @@ extern "C" int dtb_comm_all_reduce_sgd(const dtb_comm* c, size_t grad_offset, si
   const SgdArgs sgd = {param_offset, lr, 1.f - lr * weight_decay};
   auto s = static_cast<cudaStream_t>(stream);
   const bool wide = grad_offset % 32 == 0 && param_offset % 32 == 0 && (n * 2) % 32 == 0 && wide_enabled();
+  if (use_nvls(c)) {
+    if (exclusive_of(max_ctas)) DTB_CUDA_OK((launch_exclusive_nvls<false, true>(x, grad_offset, nvec, sgd, ctas_of(max_ctas), s)));
+    else allreduce_nvls_kernel<false, true, THREADS><<<pick_grid(nvec / c->world / 4 + 1, ctas_of(max_ctas), 64), THREADS, 0, s>>>(x, grad_offset, nvec, sgd);
+    DTB_LAUNCH_OK();
+    return 0;
+  }
   DISPATCH_W(c->world, {
     if (wide && exclusive_of(max_ctas)) DTB_CUDA_OK((launch_exclusive<W, true>(x, grad_offset, nvec / 2, sgd, ctas_of(max_ctas), s)));
     else if (wide) allreduce_twoshot256_kernel<W, true, THREADS><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec / 2, sgd);
@@ -585,8 +796,9 @@ extern "C" int dtb_comm_all_gather(const dtb_comm* c, size_t dst_offset, size_t 
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * esize / 16;
-  allgather_kernel<<<pick_grid(nvec, ctas_of(max_ctas), 64), THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, dst_offset, src_offset, nvec);
+  const int grid = pick_grid(nvec, ctas_of(max_ctas), 64);
+  if (use_nvls(c)) allgather_nvls_kernel<<<grid, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, dst_offset, src_offset, nvec);
+  else allgather_kernel<<<grid, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(x, dst_offset, src_offset, nvec);
   DTB_LAUNCH_OK();
   return 0;
 }
@@ -602,8 +814,11 @@ extern "C" int dtb_comm_reduce_scatter_avg(const dtb_comm* c, void* out, int out
   const int grid = pick_grid(nvec, ctas_of(max_ctas), 64);
   auto s = static_cast<cudaStream_t>(stream);
   OptArgs o = {};
+  const bool nvls = use_nvls(c);
   DISPATCH_W(c->world, {
-    if (src_dtype == 1) reduce_scatter_kernel<true, W, 0><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
+    if (src_dtype == 1 && nvls) reduce_scatter_kernel<true, W, 0, true><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
+    else if (src_dtype == 1) reduce_scatter_kernel<true, W, 0><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
+    else if (nvls) reduce_scatter_kernel<false, W, 0, true><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
     else reduce_scatter_kernel<false, W, 0><<<grid, THREADS, 0, s>>>(x, src_offset, nvec, out, out_fp32, o);
   });
   DTB_LAUNCH_OK();
@@ -626,7 +841,11 @@ extern "C" int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t s
                reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(c->peers[c->rank]) + shard_offset),
                opt, lr, beta1, beta2, eps, weight_decay, bias_corr1, bias_corr2, momentum};
   auto s = static_cast<cudaStream_t>(stream);
-  DISPATCH_W(c->world, { reduce_scatter_kernel<false, W, 1><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, nullptr, 0, o); });
+  const bool nvls = use_nvls(c);
+  DISPATCH_W(c->world, {
+    if (nvls) reduce_scatter_kernel<false, W, 1, true><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, nullptr, 0, o);
+    else reduce_scatter_kernel<false, W, 1><<<grid, THREADS, 0, s>>>(x, grad_offset, nvec, nullptr, 0, o);
+  });
   DTB_LAUNCH_OK();
   return 0;
 }

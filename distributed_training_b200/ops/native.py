@@ -449,6 +449,60 @@ def symm_free(ptr: int) -> None:
     _ok(lib().dtb_symm_free(C.c_void_p(ptr)))
 
 
+def symm_vmm_probe() -> Tuple[bool, bool]:
+    """(VMM with fd handles supported, multicast objects supported) on the current device."""
+    v, m = C.c_int(0), C.c_int(0)
+    _ok(lib().dtb_symm_vmm_probe(C.byref(v), C.byref(m)))
+    return bool(v.value), bool(m.value)
+
+
+def symm_vmm_granularity(world: int, multicast: bool) -> int:
+    g = C.c_size_t(0)
+    _ok(lib().dtb_symm_vmm_granularity(world, int(multicast), C.byref(g)))
+    return int(g.value)
+
+
+def symm_vmm_create(nbytes: int) -> Tuple[int, int]:
+    """(allocation handle, exported POSIX fd) of ``nbytes`` of device memory on the current device."""
+    h, fd = C.c_ulonglong(0), C.c_int(-1)
+    _ok(lib().dtb_symm_vmm_create(C.c_size_t(nbytes), C.byref(h), C.byref(fd)))
+    return int(h.value), int(fd.value)
+
+
+def symm_vmm_import(fd: int) -> int:
+    h = C.c_ulonglong(0)
+    _ok(lib().dtb_symm_vmm_import(int(fd), C.byref(h)))
+    return int(h.value)
+
+
+def symm_vmm_map(handle: int, nbytes: int, alignment: int = 0) -> int:
+    ptr = C.c_void_p()
+    _ok(lib().dtb_symm_vmm_map(C.c_ulonglong(handle), C.c_size_t(nbytes), C.c_size_t(alignment), C.byref(ptr)))
+    return int(ptr.value)
+
+
+def symm_vmm_unmap(ptr: int, nbytes: int) -> None:
+    _ok(lib().dtb_symm_vmm_unmap(C.c_void_p(ptr), C.c_size_t(nbytes)))
+
+
+def symm_vmm_release(handle: int) -> None:
+    _ok(lib().dtb_symm_vmm_release(C.c_ulonglong(handle)))
+
+
+def symm_mc_create(nbytes: int, world: int) -> Tuple[int, int]:
+    h, fd = C.c_ulonglong(0), C.c_int(-1)
+    _ok(lib().dtb_symm_mc_create(C.c_size_t(nbytes), world, C.byref(h), C.byref(fd)))
+    return int(h.value), int(fd.value)
+
+
+def symm_mc_add_device(mc_handle: int) -> None:
+    _ok(lib().dtb_symm_mc_add_device(C.c_ulonglong(mc_handle)))
+
+
+def symm_mc_bind(mc_handle: int, mem_handle: int, nbytes: int) -> None:
+    _ok(lib().dtb_symm_mc_bind(C.c_ulonglong(mc_handle), C.c_ulonglong(mem_handle), C.c_size_t(nbytes)))
+
+
 EXCLUSIVE = 1 << 20     # OR into max_ctas: whole-SM (1024-thread) comm CTAs instead of co-resident 256-thread ones
 
 

@@ -1,11 +1,23 @@
 """Symmetric-memory communicator for B200 (NVLink 5 / NVSwitch peer access).
 
-Every rank allocates identically sized *segments* of device memory, exports
-them through CUDA IPC and maps all peers' segments, so rank ``r``'s buffer at
-``(segment, offset)`` has a known address in every process.  Collectives are
-single kernels from ``csrc/comm/collectives.cu`` that read and write those
-peer addresses directly; ``torch.distributed`` (gloo) is used only to exchange
-the 64-byte IPC handles and for host-side scalars.
+Every rank allocates identically sized *segments* of device memory and maps
+all peers' segments, so rank ``r``'s buffer at ``(segment, offset)`` has a
+known address in every process.  Collectives are single kernels from
+``csrc/comm/collectives.cu`` that read and write those peer addresses
+directly; ``torch.distributed`` (gloo) only bootstraps (handle exchange,
+host-side scalars).
+
+Two heap back ends (``DTB200_HEAP=auto|vmm|ipc``):
+
+* **vmm** (default when the driver supports it and world > 1): segments are
+  ``cuMemCreate`` allocations exported as POSIX file descriptors; the fds are
+  passed between the ranks over Unix sockets (``SCM_RIGHTS``), imported and
+  mapped.  All ranks' pages are additionally bound to one **multicast
+  object** whose mapping (``dtb_comm.mc_base``) is the NVLS address: the
+  ``multimem.ld_reduce`` / ``multimem.st`` kernels reduce inside the NVSwitch
+  and write every replica with one store.
+* **ipc**: ``cudaMalloc`` + CUDA IPC handles (single rank, or drivers without
+  VMM/fd support).  No multicast mapping; the peer-load/store kernels run.
 
 Replaces ``ProcessGroupNCCL`` as used by the reference
 (/root/reference/src/distributed_trainer.py:61-62).
@@ -20,7 +32,9 @@ from __future__ import annotations
 
 import logging
 import os
-from dataclasses import dataclass
+import socket
+import struct
+from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -55,6 +69,50 @@ class Segment:
     desc: native.CommDesc
     used: int = 0
     base_tensor: Optional[torch.Tensor] = None
+    backend: str = "ipc"
+    mc_ptr: int = 0                       # NVLS multicast mapping of the segment (0 = none)
+    total_bytes: int = 0
+    handles: List[int] = field(default_factory=list)      # VMM allocation handles (own + imported)
+    mc_handle: int = 0
+
+
+def _fd_address(rank: int, seq: int) -> str:
+    port = os.environ.get("MASTER_PORT", "0")
+    return f"\0dtb200-{os.getuid()}-{port}-{seq}-{rank}"       # abstract namespace: nothing to unlink
+
+
+def exchange_fds(fd: Optional[int], rank: int, world: int, seq: int) -> List[Optional[int]]:
+    """All-to-all of one file descriptor per rank over Unix sockets (``SCM_RIGHTS`` -- VMM allocation handles are
+    POSIX fds, and this is the one fd transport every container allows).  ``None`` = this rank contributes nothing.
+    Returns, for every rank, that rank's descriptor as received in this process (own slot = ``fd``).  Collective over
+    the default (bootstrap) process group; ``seq`` must be the same on all ranks and fresh per call."""
+    server = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    server.bind(_fd_address(rank, seq))
+    server.listen(world)
+    dist.barrier()                                   # every server is listening
+    clients = {}
+    for q in range(world):
+        if q != rank:
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(_fd_address(q, seq))           # queues in q's backlog; q accepts below
+            clients[q] = c
+    for _ in range(world - 1):
+        conn, _addr = server.accept()
+        with conn:
+            if fd is None:
+                conn.sendall(struct.pack("i", 0))
+            else:
+                socket.send_fds(conn, [struct.pack("i", 1)], [fd])
+    out: List[Optional[int]] = [None] * world
+    out[rank] = fd
+    for q, c in clients.items():
+        with c:
+            msg, fds, _flags, _addr = socket.recv_fds(c, 4, 1)
+            has = struct.unpack("i", msg)[0] if len(msg) == 4 else 0
+            out[q] = fds[0] if (has and fds) else None
+    server.close()
+    dist.barrier()
+    return out
 
 
 class _StreamWork(Work):
@@ -108,6 +166,12 @@ class SymmComm(Communicator):
         self.stream = torch.cuda.Stream(self.device, priority=-1) if overlap_stream else None
         self._closed = False
         self._scratch: Optional[torch.Tensor] = None
+        self._preferred: Optional[Segment] = None
+        self._fd_seq = 0
+        self.backend: Optional[str] = None          # "vmm" | "ipc", decided collectively with the first segment
+        self.multicast = False
+        #: spin-watchdog budget of every collective, in SM clocks (0 = library default, ~20 s); DTB_COMM_TIMEOUT_MS
+        self.timeout_cycles = int(float(os.environ.get("DTB_COMM_TIMEOUT_MS", "0")) * 1.9e6)
 
     # ------------------------------------------------------------------ heap
     def _exchange(self, payload: bytes) -> List[bytes]:
@@ -117,39 +181,168 @@ class SymmComm(Communicator):
         dist.all_gather_object(gathered, payload)
         return [g for g in gathered]  # type: ignore[misc]
 
+    def _exchange_fds(self, fd: Optional[int]) -> List[Optional[int]]:
+        self._fd_seq += 1
+        return exchange_fds(fd, self.rank, self.world_size, self._fd_seq)
+
+    def _all_ok(self, ok: bool) -> bool:
+        if self.world_size == 1:
+            return ok
+        flags: List[Optional[bool]] = [None] * self.world_size
+        dist.all_gather_object(flags, bool(ok))
+        return all(bool(f) for f in flags)
+
+    def _pick_backend(self) -> str:
+        want = os.environ.get("DTB200_HEAP", "auto").lower()
+        if want not in ("auto", "vmm", "ipc"):
+            raise ValueError(f"DTB200_HEAP must be auto, vmm or ipc, got {want!r}")
+        if want == "ipc" or (want == "auto" and self.world_size == 1):
+            self.multicast = False
+            return "ipc"
+        vmm_ok, mc_ok = native.symm_vmm_probe()
+        vmm_all = self._all_ok(vmm_ok)
+        self.multicast = self._all_ok(mc_ok) and self.world_size > 1 and os.environ.get("DTB200_MULTICAST", "1") != "0"
+        if not vmm_all:
+            if want == "vmm":
+                raise RuntimeError("DTB200_HEAP=vmm but the driver reports no VMM / fd-handle support")
+            logger.warning("driver reports no VMM / POSIX-fd handle support: symmetric heap falls back to CUDA IPC")
+            self.multicast = False
+            return "ipc"
+        return "vmm"
+
     def _new_segment(self, min_bytes: int) -> Segment:
+        if self.backend is None:
+            self.backend = self._pick_backend()
         nbytes = max(self.segment_bytes, (min_bytes + ALIGN - 1) // ALIGN * ALIGN)
+        if self.backend == "vmm":
+            seg = self._new_segment_vmm(nbytes)
+        else:
+            seg = self._new_segment_ipc(nbytes)
+        self.segments.append(seg)
+        if self.world_size > 1:
+            dist.barrier()     # every rank has mapped every peer before the first kernel touches it
+        logger.info(f"[rank {self.rank}] symmetric segment {seg.index}: {seg.nbytes / 2**20:.0f} MiB mapped on "
+                    f"{self.world_size} ranks ({seg.backend}{', NVLS multicast' if seg.mc_ptr else ''})")
+        return seg
+
+    def _describe(self, index: int, nbytes: int, ptr: int, peer_ptrs: List[int], mc_ptr: int, backend: str) -> Segment:
+        desc = native.CommDesc()
+        for r in range(self.world_size):
+            desc.peers[r] = peer_ptrs[r]
+            desc.signals[r] = peer_ptrs[r] + nbytes
+        desc.mc_base = mc_ptr if mc_ptr else None
+        desc.rank, desc.world, desc.timeout_cycles = self.rank, self.world_size, self.timeout_cycles
+        seg = Segment(index, nbytes, ptr, peer_ptrs, [p + nbytes for p in peer_ptrs], desc, backend=backend,
+                      mc_ptr=mc_ptr, total_bytes=nbytes + native.SIGNAL_PAD_BYTES)
+        seg.base_tensor = torch.as_tensor(_RawBuffer(ptr, nbytes, seg), device=self.device)
+        return seg
+
+    def _new_segment_ipc(self, nbytes: int) -> Segment:
         total = nbytes + native.SIGNAL_PAD_BYTES
         ptr, handle = native.symm_alloc(total)       # zero-filled, synchronised
         handles = self._exchange(handle)
         peer_ptrs = []
         for r, h in enumerate(handles):
             peer_ptrs.append(ptr if r == self.rank else native.symm_open(h))
-        desc = native.CommDesc()
-        for r in range(self.world_size):
-            desc.peers[r] = peer_ptrs[r]
-            desc.signals[r] = peer_ptrs[r] + nbytes
-        desc.mc_base = None
-        desc.rank, desc.world, desc.timeout_cycles = self.rank, self.world_size, 0
-        seg = Segment(len(self.segments), nbytes, ptr, peer_ptrs, [p + nbytes for p in peer_ptrs], desc)
-        seg.base_tensor = torch.as_tensor(_RawBuffer(ptr, nbytes, seg), device=self.device)
-        self.segments.append(seg)
-        if self.world_size > 1:
-            dist.barrier()     # every rank has mapped every peer before the first kernel touches it
-        logger.info(f"[rank {self.rank}] symmetric segment {seg.index}: {nbytes / 2**20:.0f} MiB mapped on "
-                    f"{self.world_size} ranks")
+        return self._describe(len(self.segments), nbytes, ptr, peer_ptrs, 0, "ipc")
+
+    def _new_segment_vmm(self, nbytes: int) -> Segment:
+        """cuMemCreate + fd exchange + (when supported) one multicast object bound to every rank's pages."""
+        w, r = self.world_size, self.rank
+        gran = native.symm_vmm_granularity(w, self.multicast)
+        total = (nbytes + native.SIGNAL_PAD_BYTES + gran - 1) // gran * gran
+        nbytes = total - native.SIGNAL_PAD_BYTES          # the signal pad sits at the end of the rounded-up range
+        handle, fd = native.symm_vmm_create(total)
+        fds = self._exchange_fds(fd)
+        handles, peer_ptrs = [], []
+        for q in range(w):
+            h = handle if q == r else native.symm_vmm_import(fds[q])
+            handles.append(h)
+            peer_ptrs.append(native.symm_vmm_map(h, total, gran))
+            if q != r and fds[q] is not None:
+                os.close(fds[q])
+        os.close(fd)
+        ptr = peer_ptrs[r]
+        whole = torch.as_tensor(_RawBuffer(ptr, total, None), device=self.device)
+        whole.zero_()
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+        mc_ptr, mc_handle = 0, 0
+        if self.multicast:
+            mc_ptr, mc_handle = self._bind_multicast(handle, total, gran)
+        seg = self._describe(len(self.segments), nbytes, ptr, peer_ptrs, mc_ptr, "vmm")
+        seg.total_bytes, seg.handles, seg.mc_handle = total, handles, mc_handle
         return seg
 
-    def reserve(self, nbytes: int) -> None:
-        """Make sure one segment has ``nbytes`` free, so buffers allocated next share a segment."""
+    def _bind_multicast(self, mem_handle: int, total: int, gran: int) -> Tuple[int, int]:
+        """(multicast address, handle) of this segment, or (0, 0) when any rank fails a step: every rank then runs
+        the peer-load/store kernels on the unicast mappings (decided collectively, so nobody waits for a peer that
+        gave up)."""
+        w, r = self.world_size, self.rank
+        mc_handle, fd, ok = 0, None, True
+        if r == 0:
+            try:
+                mc_handle, fd = native.symm_mc_create(total, w)
+            except RuntimeError as exc:
+                logger.warning(f"cuMulticastCreate failed ({exc}); NVLS disabled")
+                ok = False
+        if not self._all_ok(ok):
+            self.multicast = False
+            return 0, 0
+        fds = self._exchange_fds(fd)
+        stage = "import"
+        try:
+            if r != 0:
+                mc_handle = native.symm_vmm_import(fds[0])
+                os.close(fds[0])
+            else:
+                os.close(fd)
+            stage = "add_device"
+            native.symm_mc_add_device(mc_handle)
+        except RuntimeError as exc:
+            logger.warning(f"[rank {r}] multicast {stage} failed ({exc}); NVLS disabled")
+            ok = False
+        if not self._all_ok(ok):            # also the barrier "every device was added" that must precede binding
+            self.multicast = False
+            return 0, 0
+        mc_ptr = 0
+        try:
+            native.symm_mc_bind(mc_handle, mem_handle, total)
+            mc_ptr = native.symm_vmm_map(mc_handle, total, gran)
+        except RuntimeError as exc:
+            logger.warning(f"[rank {r}] multicast bind/map failed ({exc}); NVLS disabled")
+            ok = False
+        if not self._all_ok(ok):
+            self.multicast = False
+            return 0, 0
+        return mc_ptr, mc_handle
+
+    @property
+    def nvls_active(self) -> bool:
+        """True when the bandwidth-bound collectives run on the multimem (NVLS) kernels: a multicast mapping exists
+        and the library's policy (``use_nvls`` in collectives.cu: world >= 4, or ``DTB_COMM_NVLS=1``) selects them."""
+        mode = os.environ.get("DTB_COMM_NVLS", "")
+        if not self.multicast or self.world_size < 2 or mode == "0":
+            return False
+        return mode == "1" or self.world_size >= 4
+
+    def reserve(self, nbytes: int) -> Segment:
+        """Make sure ONE segment has ``nbytes`` free and make it the preferred segment of the allocations that
+        follow, so buffers a fused kernel addresses by offset (gradient bucket + parameters, shard + full weight +
+        gradient) end up in the same segment even when older segments still have holes."""
         nbytes = (nbytes + ALIGN - 1) // ALIGN * ALIGN
-        if not any(s.nbytes - s.used >= nbytes for s in self.segments):
-            self._new_segment(nbytes)
+        seg = next((s for s in self.segments if s.nbytes - s.used >= nbytes), None)
+        if seg is None:
+            seg = self._new_segment(nbytes)
+        self._preferred = seg
+        return seg
 
     def alloc(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
         esize = torch.empty((), dtype=dtype).element_size()
         nbytes = (numel * esize + ALIGN - 1) // ALIGN * ALIGN
-        seg = next((s for s in self.segments if s.nbytes - s.used >= nbytes), None)
+        order = ([self._preferred] if self._preferred is not None else []) + \
+            [s for s in self.segments if s is not self._preferred]
+        seg = next((s for s in order if s.nbytes - s.used >= nbytes), None)
         if seg is None:
             seg = self._new_segment(nbytes)
         offset = seg.used
@@ -341,7 +534,12 @@ class SymmComm(Communicator):
             for r, p in enumerate(seg.peer_ptrs):
                 if r != self.rank:
                     try:
-                        native.symm_close(p)
+                        if seg.backend == "vmm":
+                            native.symm_vmm_unmap(p, seg.total_bytes)
+                            native.symm_vmm_release(seg.handles[r])
+                        else:
+                            native.symm_close(p)
                     except Exception:  # pragma: no cover
                         pass
-        # the local allocations are released at process exit: live tensors may still point into them
+        # the local allocations (and the multicast mapping of them) are released at process exit: live tensors may
+        # still point into them

@@ -204,18 +204,24 @@ int dtb_multi_tensor_adamw(const dtb_mt_args* args, float lr, float beta1, float
 typedef struct dtb_comm {
   void* peers[DTB_MAX_RANKS];
   uint32_t* signals[DTB_MAX_RANKS];
-  void* mc_base;          /* NVLS multicast mapping of the heap, or NULL */
+  void* mc_base;          /* NVLS multicast mapping of the same segment (dtb_symm_mc_*), or NULL */
   int rank, world;
-  long long timeout_cycles; /* spin watchdog (0 = default); on expiry the kernel sets an error flag and exits */
+  long long timeout_cycles; /* spin watchdog in SM clocks (0 = default, ~20 s).  On expiry the waiting CTA records the
+                             * missing peer in the communicator's error slot and leaves the kernel without touching the
+                             * payload; later collectives on the communicator return at entry; dtb_comm_error_flag()
+                             * reports it to the host. */
 } dtb_comm;
 /* all ranks enter; returns when every rank's prior work on `stream` is visible to peers */
 int dtb_comm_barrier(const dtb_comm* c, int channel, void* stream);
 /* buf[offset .. +bytes) on every rank = root's */
 int dtb_comm_broadcast(const dtb_comm* c, size_t offset, size_t bytes, int root, int max_ctas, void* stream);
-/* in-place mean over ranks of n elements at `offset` (dtype: 0 bf16, 1 fp32); algo: 0 auto, 1 one-shot,
- * 2 two-shot.  3 is reserved for an NVLS (multimem) variant and is rejected with an error in this build: the
- * symmetric heap is cudaMalloc + CUDA IPC, which cannot be bound to a multicast object.  OR 1<<20 into max_ctas to
- * run a large bf16 two-shot reduction on whole-SM 1024-thread CTAs (the caller must have left that many SMs free). */
+/* in-place mean over ranks of n elements at `offset` (dtype: 0 bf16, 1 fp32); algo: 0 auto, 1 one-shot (peer loads),
+ * 2 two-shot (peer loads + peer stores, fixed rank order: bit-identical to a sequential fp32 sum), 3 NVLS two-shot
+ * (multimem.ld_reduce + multimem.st through the NVSwitch; needs c->mc_base; identical on all ranks, summation order
+ * chosen by the switch).  auto = one-shot up to 64 KiB, else NVLS when c->mc_base is mapped and world >= 4
+ * (DTB_COMM_NVLS=0/1 overrides), else two-shot.  The same rule selects the multimem variants of broadcast,
+ * all-gather, reduce-scatter and rs_optim.  OR 1<<20 into max_ctas to run a large two-shot / NVLS reduction on
+ * whole-SM 1024-thread CTAs (the caller must have left that many SMs free). */
 int dtb_comm_all_reduce_avg(const dtb_comm* c, size_t offset, long long n, int dtype, int algo, int max_ctas,
                             void* stream);
 /* Gradient all-reduce fused with the optimizer step (bf16): rank r averages slice r of the gradients over
@@ -251,11 +257,32 @@ int dtb_debug_stream_probe(const void* a, const void* b, void* p, void* q, long 
 int dtb_comm_error_flag(const dtb_comm* c);
 
 /* ---- host-side helpers for the symmetric heap --------------------------------- */
-/* cudaMalloc + cudaIpcGetMemHandle; handle_out must hold 64 bytes. Allocates device memory. */
+/* CUDA IPC back end: cudaMalloc + cudaIpcGetMemHandle; handle_out must hold 64 bytes. Allocates device memory. */
 int dtb_symm_alloc(size_t bytes, void** ptr_out, void* handle_out);
 int dtb_symm_open(const void* handle, void** ptr_out);
 int dtb_symm_close(void* ptr);
 int dtb_symm_free(void* ptr);
+/* VMM + NVLS back end (what NCCL's NVLS transport sets up for the reference, /root/reference/src/distributed_trainer.py:60-62).
+ * All calls act on the CURRENT device.  Bootstrap of one segment (parallel/symm.py):
+ *   every rank : granularity -> create (physical memory + POSIX fd) -> send the fd to every peer (SCM_RIGHTS)
+ *                -> import each peer's fd -> map own and peers' handles (unicast addresses = dtb_comm.peers[])
+ *   rank 0     : mc_create (multicast object + fd) -> send the fd to every peer;  peers: import
+ *   every rank : mc_add_device -> [host barrier] -> mc_bind(own memory) -> [host barrier] -> map(mc handle)
+ *                = dtb_comm.mc_base.
+ * probe: *vmm_ok = the driver supports VMM with fd handles; *multicast_ok = and multicast objects. */
+int dtb_symm_vmm_probe(int* vmm_ok, int* multicast_ok);
+int dtb_symm_vmm_granularity(int world, int multicast, size_t* gran_out);
+/* cuMemCreate (allocates device memory) + export; the caller closes the fd once the peers have imported it */
+int dtb_symm_vmm_create(size_t bytes, unsigned long long* handle_out, int* fd_out);
+int dtb_symm_vmm_import(int fd, unsigned long long* handle_out);
+/* reserve a VA range, map `handle` (memory or multicast) into it, grant this device read/write */
+int dtb_symm_vmm_map(unsigned long long handle, size_t bytes, size_t alignment, void** ptr_out);
+int dtb_symm_vmm_unmap(void* ptr, size_t bytes);
+int dtb_symm_vmm_release(unsigned long long handle);
+int dtb_symm_mc_create(size_t bytes, int world, unsigned long long* handle_out, int* fd_out);
+int dtb_symm_mc_add_device(unsigned long long mc_handle);
+int dtb_symm_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t bytes);
+int dtb_symm_mc_unbind(unsigned long long mc_handle, size_t bytes);
 
 #ifdef __cplusplus
 }

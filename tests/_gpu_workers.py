@@ -24,13 +24,31 @@ def _gather_cpu(t, world):
     return out
 
 
-def collectives(rank, world, port, out_dir):
+def _same(comm, got, expect, what):
+    """Peer-load kernels sum in fixed rank order in fp32: bit-identical to the sequential oracle.  The NVLS kernels
+    sum inside the switch (fp32, order chosen by the hardware): equal to the oracle up to one rounding step."""
+    if comm.nvls_active:
+        tol = 2 ** -7 if expect.dtype == torch.bfloat16 else 1e-6
+        assert torch.allclose(got.float(), expect.float(), rtol=tol, atol=tol * 4), \
+            (what, (got.float() - expect.float()).abs().max())
+    else:
+        assert torch.equal(got, expect), (what, (got.float() - expect.float()).abs().max())
+
+
+def collectives(rank, world, port, out_dir, nvls="auto"):
+    if nvls != "auto":
+        os.environ["DTB_COMM_NVLS"] = str(nvls)         # read once by the library, before its first collective
     from distributed_training_b200.parallel.symm import SymmComm
 
     _init(rank, world, port)
     comm = SymmComm(torch.device("cuda", rank), segment_bytes=256 << 20)
     try:
         dev = comm.device
+        comm.reserve(1 << 20)
+        if nvls == "1" and not comm.multicast:
+            torch.save({"ok": True, "skipped": "no multicast support on this box"}, os.path.join(out_dir, f"ok{rank}.pt"))
+            return
+        assert comm.nvls_active == (comm.multicast and (nvls == "1" or (nvls == "auto" and world >= 4)))
         # ---- all-reduce: one-shot and two-shot sizes, both dtypes, repeated (flag reuse) ----
         for dtype in (torch.float32, torch.bfloat16):
             for n in (21, 1000, 16 * 1024, 300_000, 4_000_000 + 8):
@@ -45,7 +63,10 @@ def collectives(rank, world, port, out_dir):
                     for r in range(world):                    # fixed rank order, fp32, like the kernel
                         acc += per_rank[r].float()
                     expect = (acc / world).to(dtype)
-                    assert torch.equal(buf.cpu(), expect), (dtype, n, rep, (buf.cpu().float() - expect.float()).abs().max())
+                    if n * buf.element_size() <= 64 << 10:        # one-shot (peer loads): always exact
+                        assert torch.equal(buf.cpu(), expect), (dtype, n, rep)
+                    else:
+                        _same(comm, buf.cpu(), expect, (dtype, n, rep))
                     got = _gather_cpu(buf, world)
                     assert all(torch.equal(got[0], t) for t in got), "ranks disagree bitwise"
         # ---- copy-engine path (what large buckets take): same contract; threshold lowered so small buffers use it ----
@@ -96,7 +117,7 @@ def collectives(rank, world, port, out_dir):
                 buf.copy_(per_rank[rank])
                 comm.all_reduce_avg_(buf).wait()
                 torch.cuda.synchronize()
-                assert torch.equal(buf.cpu(), mean.to(torch.bfloat16)), ("exclusive mean", n, rep)
+                _same(comm, buf.cpu(), mean.to(torch.bfloat16), ("exclusive mean", n, rep))
                 buf.copy_(per_rank[rank])
                 par.copy_(p0)
                 comm.all_reduce_sgd_(buf, par, 0.05, 0.01).wait()
@@ -130,10 +151,14 @@ def collectives(rank, world, port, out_dir):
         acc = torch.zeros(n)
         for r in range(world):
             acc += per_rank[r][rank * n:(rank + 1) * n].float()
-        assert torch.allclose(out.cpu(), acc / world, atol=1e-6)
+        if comm.nvls_active:       # the switch hands back the bf16-rounded sum
+            assert torch.allclose(out.cpu(), acc / world, rtol=2 ** -7, atol=1e-3)
+        else:
+            assert torch.allclose(out.cpu(), acc / world, atol=1e-6)
         comm.barrier()
         comm.check_errors()
-        torch.save({"ok": True}, os.path.join(out_dir, f"ok{rank}.pt"))
+        torch.save({"ok": True, "backend": comm.backend, "multicast": comm.multicast, "nvls": comm.nvls_active},
+                   os.path.join(out_dir, f"ok{rank}.pt"))
     finally:
         comm.close()
         dist.destroy_process_group()

@@ -14,10 +14,17 @@ def _world():
     return 8 if n >= 8 else (4 if n >= 4 else 2)
 
 
-def test_collectives_exact_and_bitwise_identical(tmp_path):
+@pytest.mark.parametrize("nvls", ["0", "1"])
+def test_collectives_exact_and_bitwise_identical(tmp_path, nvls):
+    """nvls=0: peer-load/store kernels (bit-exact vs a fixed-order fp32 sum); nvls=1: multimem kernels on the
+    multicast mapping (identical on every rank, equal to the oracle within one rounding)."""
     w = _world()
-    mp.spawn(G.collectives, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
+    mp.spawn(G.collectives, args=(w, free_port(), str(tmp_path), nvls), nprocs=w, join=True)
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(w))
+    res = torch.load(tmp_path / "ok0.pt", weights_only=False)
+    if res.get("skipped"):
+        pytest.skip(res["skipped"])
+    assert res["nvls"] == (nvls == "1")
 
 
 def test_native_ddp_step_matches_single_process(tmp_path):
