@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--depth", type=int, default=DEPTH)
     ap.add_argument("--comm-ctas", type=int, default=0)
     ap.add_argument("--comm-ce", type=int, default=-1, help="1/0: copy-engine path for large all-reduces")
+    ap.add_argument("--loader-workers", type=int, default=2, help="ShardedLoader gather threads in the e2e loop")
     ap.add_argument("--comm-exclusive", type=int, default=-1,
                     help="whole-SM comm CTAs for large all-reduces (0 = co-resident mode, -1 = library default)")
     return ap.parse_args()
@@ -65,14 +66,16 @@ def dist_env(args):
     return rank, local_rank, world
 
 
-def pinned_pool(batch, width, n=4, seed=0):
+def device_pool(batch, width, device, n=4, seed=0):
+    """``n`` device-resident batches for the device-timed loop; seeded per rank so that ranks reduce DIFFERENT
+    gradients (the loss after K steps then depends on N)."""
     import torch
 
     g = torch.Generator().manual_seed(seed)
     pool = []
     for _ in range(n):
-        x = torch.randn(batch, width, generator=g).to(torch.bfloat16).pin_memory()
-        y = torch.randint(0, width, (batch,), generator=g, dtype=torch.int64).pin_memory()
+        x = torch.randn(batch, width, generator=g).to(torch.bfloat16).to(device)
+        y = torch.randint(0, width, (batch,), generator=g, dtype=torch.int64).to(device)
         pool.append((x, y))
     return pool
 
@@ -131,8 +134,7 @@ def run_ours(args):
         strategy.comm.exclusive_sms = args.comm_exclusive
     assert trainer.model.native_step, "the native tcgen05 path must be the one that runs"
 
-    pool = pinned_pool(args.batch, args.width)
-    dev_pool = [(x.to(device), y.to(device)) for x, y in pool]
+    dev_pool = device_pool(args.batch, args.width, device, seed=1000 + rank)
 
     def step_dev(i):
         x, y = dev_pool[i % len(dev_pool)]
@@ -151,30 +153,47 @@ def run_ours(args):
     exposed = trainer.model.exposed_comm_ms() if hasattr(trainer.model, "exposed_comm_ms") else 0.0
     exposed = max_over_ranks(exposed)
     loss_val = float(trainer.last_loss)
+    del dev_pool
 
-    # end to end through the public API: pinned host batch -> H2D -> step -> D2H loss, every step
-    def step_e2e(i):
-        x, y = pool[i % len(pool)]
-        loss = trainer.train_step(x, y)
-        return loss.item()
+    # End to end = the body of Trainer._run_epoch over the framework's own data path, the same role the reference
+    # arm's loop plays over the reference's DataLoader: a map-style dataset (sample i = row i % 8192 of a pool, as in
+    # the reference arm), rank-sharded by ShardedSampler, batches assembled by ShardedLoader (index_select into pinned
+    # staging by worker threads -> H2D on a copy stream), then _run_batch and a device->host read of the loss.
+    from distributed_training_b200.data import PooledWideDataset
+    from distributed_training_b200.trainer import prepare_dataloader
 
-    for i in range(2):
-        step_e2e(i)
-    barrier_sync()
+    e2e_warm = 3
+    e2e_steps = args.steps + e2e_warm
+    dataset = PooledWideDataset(e2e_steps * args.batch * world, args.width, args.width, torch.bfloat16)
+    loader = prepare_dataloader(dataset, args.batch, device=device, seed=0, num_workers=args.loader_workers)
+    trainer.train_data = loader
+    loader.sampler.set_epoch(0)
+    timed, h2d = 0, 0
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    start.record()
-    for i in range(args.steps):
-        step_e2e(i)
+    for i, (source, targets) in enumerate(trainer.train_data):
+        if i == e2e_warm:
+            barrier_sync()
+            start.record()
+        h2d = source.numel() * source.element_size() + targets.numel() * targets.element_size()
+        loss = trainer._run_batch(source, targets)
+        loss.item()
+        timed += int(i >= e2e_warm)
     stop.record()
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks(start.elapsed_time(stop))
     barrier_sync()
+    trainer.check_comm_errors()
 
     if rank == 0:
-        x, y = pool[0]
-        line = result_line(args, world, total_ms / args.steps, e2e_ms / args.steps, clocks, launches, "ours",
-                           x.numel() * x.element_size() + y.numel() * y.element_size(), 4,
-                           extra={"exposed_comm_ms_per_step": exposed, "final_loss": loss_val})
+        comm = strategy.comm
+        line = result_line(args, world, total_ms / args.steps, e2e_ms / max(timed, 1), clocks, launches, "ours",
+                           h2d, 4,
+                           extra={"exposed_comm_ms_per_step": exposed, "final_loss": loss_val,
+                                  "comm": {"heap": getattr(comm, "backend", None),
+                                           "nvls": bool(getattr(comm, "nvls_active", False)),
+                                           "exclusive_sms": getattr(comm, "exclusive_sms", 0)},
+                                  "e2e_path": "PooledWideDataset -> ShardedSampler -> ShardedLoader(pinned, "
+                                              f"{args.loader_workers} worker threads) -> Trainer._run_batch -> loss.item()"})
         print(json.dumps(line), flush=True)
     if strategy.comm is not None:
         strategy.comm.close()

@@ -109,20 +109,20 @@ def main():
         nbytes = min(256 << 20, (ns.max_mb << 20) // 2)
         peer = (rank + 1) % world
         local = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-        remote = torch.as_tensor(_Raw(seg.peer_ptrs[peer] + base_off, nbytes), device="cuda")
-        mine = big.view(torch.uint8)[:nbytes]
+        remote_ptr = seg.peer_ptrs[peer] + base_off
 
         def ce_pull():
-            local.copy_(remote)
+            native.debug_memcpy_async(local.data_ptr(), remote_ptr, nbytes)
 
         def ce_push():
-            remote.copy_(local)
+            native.debug_memcpy_async(remote_ptr, local.data_ptr(), nbytes)
 
         for name, fn in (("copy_engine_pull", ce_pull), ("copy_engine_push", ce_push)):
             for _ in range(2):
                 fn()
             t = timed(fn, 10)
-            emit({"p2p": name, "bytes": nbytes, "gbs_per_direction": round(nbytes / 1e6 / t, 1), "world": world})
+            emit({"p2p": name, "bytes": nbytes, "gbs_per_direction": round(nbytes / 1e6 / t, 1), "world": world,
+                  "note": "every rank copies from/to rank+1 at the same time"})
         # SM-issued peer loads: the broadcast / all-gather kernels give the one-direction inbound rates
         n16 = nbytes // world // 16 * 16
         fn = lambda: native.comm_broadcast(seg.desc, base_off, nbytes, 0, ns.ctas)
@@ -138,16 +138,9 @@ def main():
         t = timed(fn, 10)
         emit({"p2p": "all_gather", "bytes_out": n16 * world, "gbs_inbound_per_gpu": round(n16 * (world - 1) / 1e6 / t, 1),
               "world": world, "nvls": comm.nvls_active})
-        del mine
     comm.check_errors()
     comm.close()
     dist.destroy_process_group()
-
-
-class _Raw:
-    def __init__(self, ptr, nbytes):
-        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2,
-                                         "strides": None}
 
 
 if __name__ == "__main__":

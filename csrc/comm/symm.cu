@@ -319,3 +319,10 @@ extern "C" int dtb_symm_mc_unbind(unsigned long long mc_handle, size_t bytes) {
   DTB_CU_OK(api().MulticastUnbind(mc_handle, dev, 0, bytes));
   return 0;
 }
+
+// Plain cudaMemcpyAsync between any two mapped addresses (local or peer): the copy-engine rate bench/allreduce_sweep.py
+// records as the NVLink denominator.
+extern "C" int dtb_debug_memcpy_async(void* dst, const void* src, size_t bytes, void* stream) {
+  DTB_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, static_cast<cudaStream_t>(stream)));
+  return 0;
+}

@@ -13,11 +13,16 @@ Parity targets
   (/root/reference/src/distributed_trainer.py:204-211).
 * ``ShardedLoader`` replaces ``DataLoader``: whole batches are gathered with one
   ``index_select`` into pinned staging buffers and copied with
-  ``non_blocking=True`` one batch ahead of the consumer.
+  ``non_blocking=True`` ahead of the consumer.  With
+  ``num_workers > 0`` (the playground's ``--num-workers``,
+  /root/reference/src/playground/ddp_script.py:127-132,205-210) the gather and
+  the host-to-device copy run in background threads, ``prefetch`` batches ahead.
 """
 from __future__ import annotations
 
 import math
+import queue
+from concurrent.futures import Future, ThreadPoolExecutor
 from typing import Iterator, List, Optional, Sequence, Tuple
 
 import torch
@@ -82,6 +87,30 @@ class WideDataset(TensorPairDataset):
         gen = torch.Generator().manual_seed(int(seed))
         self.inputs = torch.randn(size, features, generator=gen).to(dtype)
         self.targets = torch.randint(0, num_classes, (size,), generator=gen, dtype=torch.int64)
+
+
+class PooledWideDataset(TensorPairDataset):
+    """``size`` classification samples drawn (index modulo ``pool``) from a fixed pool of rows, so a benchmark of
+    any length fits in host memory; sample ``i`` is row ``i % pool`` (the same construction as the reference arm's
+    ``baseline.models.PooledClassificationDataset``)."""
+
+    def __init__(self, size: int, features: int = 8192, num_classes: int = 8192,
+                 dtype: torch.dtype = torch.bfloat16, pool: int = 8192, seed: int = 0) -> None:
+        gen = torch.Generator().manual_seed(int(seed))
+        self.size = int(size)
+        self.inputs = torch.randn(pool, features, generator=gen).to(dtype)
+        self.targets = torch.randint(0, num_classes, (pool,), generator=gen, dtype=torch.int64)
+
+    def __len__(self) -> int:
+        return self.size
+
+    def __getitem__(self, index: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        j = int(index) % int(self.inputs.shape[0])
+        return self.inputs[j], self.targets[j]
+
+    def remap(self, idx: torch.Tensor) -> torch.Tensor:
+        """Dataset indices -> rows of ``tensors()`` (the loader's batched gather uses this)."""
+        return idx % int(self.inputs.shape[0])
 
 
 class TokenDataset(TensorPairDataset):
@@ -152,15 +181,17 @@ class ShardedSampler(Sampler[int]):
 class ShardedLoader:
     """Batch iterator over a :class:`TensorPairDataset` shard.
 
-    On CUDA the next batch is gathered into pinned host memory and its
-    host-to-device copy is issued on a side stream while the current batch is
-    being consumed; the consumer stream waits on the copy's event, never on
-    the host.  ``device=None`` yields CPU batches (the ``Trainer`` moves them).
+    On CUDA every batch is gathered into pinned host memory and its host-to-device copy is issued on a side stream
+    ahead of the consumer; the consumer stream waits on the copy's event, never on the host.
+    ``num_workers = 0``: the gather of batch i+1 runs in the consuming thread while batch i is in flight (double
+    buffer).  ``num_workers > 0``: that many background threads gather and copy up to ``prefetch`` batches ahead, so
+    a 67 MB/step input stream (wide-MLP config) costs the training thread nothing.
+    ``device=None`` yields CPU batches (the ``Trainer`` moves them).
     """
 
     def __init__(self, dataset: Dataset, batch_size: int, sampler: Optional[ShardedSampler] = None,
                  device: Optional[torch.device] = None, drop_last: bool = False,
-                 pin_memory: Optional[bool] = None) -> None:
+                 pin_memory: Optional[bool] = None, num_workers: int = 0, prefetch: int = 3) -> None:
         self.dataset = dataset
         self.batch_size = int(batch_size)
         self.sampler = sampler if sampler is not None else ShardedSampler(dataset, 1, 0, shuffle=False)
@@ -168,8 +199,11 @@ class ShardedLoader:
         self.drop_last = drop_last
         cuda = self.device is not None and self.device.type == "cuda"
         self.pin_memory = cuda if pin_memory is None else (pin_memory and torch.cuda.is_available())
+        self.num_workers = max(int(num_workers), 0)
+        self.prefetch = max(int(prefetch), 1)
         self._copy_stream = torch.cuda.Stream(self.device) if cuda else None
-        self._staging: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None, None]
+        self._staging: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None] * (self.prefetch + 1 if self.num_workers else 2)
+        self._pool: Optional[ThreadPoolExecutor] = None
 
     def __len__(self) -> int:
         n = len(self.sampler)
@@ -178,6 +212,8 @@ class ShardedLoader:
     def _gather(self, idx: torch.Tensor, slot: int) -> Tuple[torch.Tensor, torch.Tensor]:
         if hasattr(self.dataset, "tensors"):
             xs, ys = self.dataset.tensors()  # type: ignore[attr-defined]
+            if hasattr(self.dataset, "remap"):
+                idx = self.dataset.remap(idx)  # type: ignore[attr-defined]
             if self.pin_memory and idx.numel() == self.batch_size:
                 if self._staging[slot] is None:
                     self._staging[slot] = (
@@ -204,13 +240,19 @@ class ShardedLoader:
             event.record(self._copy_stream)
         return out, event
 
-    def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+    def _chunks(self) -> List[torch.Tensor]:
         order = self.sampler.indices() if hasattr(self.sampler, "indices") else torch.tensor(list(self.sampler))
         chunks = list(order.split(self.batch_size))
         if self.drop_last and chunks and chunks[-1].numel() < self.batch_size:
             chunks.pop()
+        return chunks
+
+    def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        if self.num_workers > 0:
+            yield from self._iter_threaded()
+            return
         pending = None
-        for i, idx in enumerate(chunks):
+        for i, idx in enumerate(self._chunks()):
             if self._copy_stream is not None and self._staging[i % 2] is not None:
                 # the staging slot is reused every second batch: its previous copy must be done
                 self._copy_stream.synchronize()
@@ -220,6 +262,49 @@ class ShardedLoader:
             pending = nxt
         if pending is not None:
             yield self._release(pending)
+
+    # ---- background workers ---------------------------------------------------------------------------------
+    def _produce(self, idx: torch.Tensor, free_slots: "queue.Queue[int]"):
+        """Worker-thread body: take a staging slot, gather the batch into it, copy it to the device, and hand the
+        slot back once the copy has finished (so it can be overwritten)."""
+        if self.device is not None and self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+        slot = free_slots.get()
+        try:
+            batch, event = self._to_device(self._gather(idx, slot))
+            if event is not None:
+                event.synchronize()
+        finally:
+            free_slots.put(slot)
+        if self.device is None or self._copy_stream is None:
+            # CPU consumer: the staging slot will be reused, so hand out an owning copy
+            batch = (batch[0].clone(), batch[1].clone()) if self.pin_memory else batch
+        return batch, event
+
+    def _iter_threaded(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        if self._pool is None:
+            self._pool = ThreadPoolExecutor(max_workers=self.num_workers, thread_name_prefix="dtb200-loader")
+        chunks = self._chunks()
+        free_slots: "queue.Queue[int]" = queue.Queue()
+        for s in range(len(self._staging)):
+            free_slots.put(s)
+        inflight: List[Future] = []
+        nxt = 0
+        try:
+            while nxt < len(chunks) or inflight:
+                while nxt < len(chunks) and len(inflight) < self.prefetch:
+                    inflight.append(self._pool.submit(self._produce, chunks[nxt], free_slots))
+                    nxt += 1
+                yield self._release(inflight.pop(0).result())
+        finally:
+            for f in inflight:
+                f.cancel()
+            for f in inflight:
+                if not f.cancelled():
+                    try:
+                        f.result()
+                    except Exception:  # pragma: no cover - shutdown path
+                        pass
 
     def _release(self, pending):
         batch, event = pending

@@ -567,5 +567,9 @@ def debug_stream_probe(a, b, p, q, nbytes: int, ctas: int):
     _ok(lib().dtb_debug_stream_probe(_p(a), _p(b), _p(p), _p(q), C.c_longlong(nbytes), ctas, _stream()))
 
 
+def debug_memcpy_async(dst_ptr: int, src_ptr: int, nbytes: int, stream: Optional[int] = None) -> None:
+    _ok(lib().dtb_debug_memcpy_async(C.c_void_p(dst_ptr), C.c_void_p(src_ptr), C.c_size_t(nbytes), _stream(stream)))
+
+
 def comm_error_flag(desc: CommDesc) -> int:
     return int(lib().dtb_comm_error_flag(C.byref(desc)))

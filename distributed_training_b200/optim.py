@@ -62,6 +62,16 @@ class _FusedBase(torch.optim.Optimizer):
     def _apply(self, group, params: List[torch.Tensor], t: int) -> None:  # pragma: no cover - interface
         raise NotImplementedError
 
+    def state_dict(self) -> Dict[str, Any]:
+        sd = super().state_dict()
+        sd["fused_step_count"] = self._step_count      # AdamW bias correction must continue, not restart at t = 1
+        return sd
+
+    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
+        state_dict = dict(state_dict)
+        self._step_count = int(state_dict.pop("fused_step_count", self._step_count))
+        super().load_state_dict(state_dict)
+
     def zero_grad(self, set_to_none: bool = False) -> None:  # keep bucket views attached
         if set_to_none:
             return super().zero_grad(set_to_none=True)

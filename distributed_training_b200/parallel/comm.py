@@ -104,6 +104,17 @@ class Communicator(ABC):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def gather_to_root(self, t: torch.Tensor, root: int = 0) -> Optional[List[torch.Tensor]]:
+        """Host-side gather of equally shaped tensors over the bootstrap process group: rank ``root`` gets the list
+        of every rank's tensor (CPU copies), the others ``None``.  Checkpointing only -- never on the step path."""
+        if self.world_size == 1 or not dist.is_initialized():
+            return [t.detach().to("cpu", copy=True)]
+        on_cpu = "gloo" in str(dist.get_backend())
+        src = t.detach().contiguous().to("cpu" if on_cpu else self.device)
+        out = [torch.empty_like(src) for _ in range(self.world_size)] if self.rank == root else None
+        dist.gather(src, out, dst=root)
+        return [o.cpu() for o in out] if out is not None else None
+
     def close(self) -> None:
         return None
 

@@ -83,7 +83,6 @@ class ReplicatedModule(nn.Module):
         self._index_of: Dict[int, int] = {id(p): i for i, p in enumerate(self._params)}
         if init_sync:
             self.verify_replicas()
-            self.sync_parameters()
 
         plans = plan_buckets(self._params, int(bucket_cap_mb * (1 << 20)),
                              int(first_bucket_mb * (1 << 20)), reverse=True, grad_dtype=grad_dtype)
@@ -106,6 +105,10 @@ class ReplicatedModule(nn.Module):
             self.buckets.append(bucket)
             for idx in plan.param_indices:
                 self._bucket_of[idx] = bucket
+        if init_sync:
+            # after re-homing: heap-resident parameter buffers are broadcast in place (one kernel per bucket, no
+            # staging copies); buffers and parameters outside the heap go through a staging slab
+            self.sync_parameters()
         self._optimizer: Any = None
         self._hook_handles = []
         for i, p in enumerate(self._params):
@@ -136,7 +139,11 @@ class ReplicatedModule(nn.Module):
 
     def sync_parameters(self, src: int = 0) -> None:
         """Broadcast rank ``src``'s parameters and buffers (DDP init sync)."""
-        tensors = [p.data for p in self.module.parameters()] + [b.data for b in self.module.buffers()]
+        homed = {id(p) for b in getattr(self, "buckets", []) if b.param_buffer is not None
+                 for p in (self._params[i] for i in b.plan.param_indices)}
+        tensors = [b.param_buffer for b in getattr(self, "buckets", []) if b.param_buffer is not None]
+        tensors += [p.data for p in self.module.parameters() if id(p) not in homed]
+        tensors += [b.data for b in self.module.buffers()]
         self.comm.broadcast_(tensors, src=src)
 
     def attach_grad_views(self) -> None:

@@ -338,14 +338,33 @@ class ShardedOptimizer:
         return None
 
     def state_dict(self) -> Dict[str, Any]:
-        return {"step": self.step_count, "rank": self.model.comm.rank,
-                "state": {k: {n: t.cpu() for n, t in v.items()} for k, v in self.state.items()}}
+        """COLLECTIVE (every rank must call it): the unsharded optimizer state -- each unit's fp32 master and
+        moments concatenated over ranks in shard order -- on rank 0; other ranks get an empty ``state``.  The file
+        can therefore be loaded at any world size (``load_state_dict`` re-slices it)."""
+        comm = self.model.comm
+        full: Dict[str, Dict[str, torch.Tensor]] = {}
+        for unit in self.model.units:
+            for n, t in self.state[unit.name].items():
+                parts = comm.gather_to_root(t)
+                if parts is not None:
+                    full.setdefault(unit.name, {})[n] = torch.cat([p.view(-1) for p in parts])
+        return {"step": self.step_count, "format": "full", "world_size": comm.world_size, "state": full}
 
     def load_state_dict(self, sd: Dict[str, Any]) -> None:
+        """Every rank loads the same full-state dict and keeps its own slice."""
+        if sd.get("format") != "full":
+            raise ValueError("sharded optimizer state must be a full-state dict written by ShardedOptimizer.state_dict "
+                             "(per-rank shard dumps of earlier versions cannot be re-sharded)")
         self.step_count = int(sd["step"])
-        for k, v in sd["state"].items():
-            for n, t in v.items():
-                self.state[k][n].copy_(t)
+        rank = self.model.comm.rank
+        for unit in self.model.units:
+            n = unit.shard_numel
+            for name, t in sd["state"].get(unit.name, {}).items():
+                dst = self.state[unit.name][name]
+                flat = t.view(-1)
+                piece = flat[rank * n: (rank + 1) * n]
+                dst.zero_()
+                dst[: piece.numel()].copy_(piece)
 
 
 class FSDPStrategy(DistributedStrategy):

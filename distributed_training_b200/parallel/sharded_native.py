@@ -201,7 +201,11 @@ class NativeShardedModule(nn.Module):
         sw.gathered = False            # the shards changed: `full` is stale until the next gather
 
     def forward_backward(self, inputs: torch.Tensor, targets: torch.Tensor, **kwargs: Any) -> torch.Tensor:
-        kwargs.pop("loss", None)
+        loss = kwargs.pop("loss", None)
+        if loss is not None and "loss" in getattr(self.inner.forward_backward, "__code__", type("c", (), {"co_varnames": ()})).co_varnames:
+            kwargs["loss"] = loss          # the model validates it (train.loss reaches the native step)
+        elif loss not in (None, "cross_entropy"):
+            raise ValueError(f"{type(self.inner).__name__}'s native step trains with cross_entropy; got loss={loss!r}")
         for sw in self.weights.values():
             sw.updated = False
         loss = self.inner.forward_backward(inputs, targets, grad_sink=self, **kwargs)
@@ -278,21 +282,38 @@ class NativeShardedOptimizer:
         return None
 
     def state_dict(self) -> Dict[str, Any]:
+        """COLLECTIVE (every rank must call it): full optimizer state on rank 0 -- per sharded weight the ``[N, K]``
+        fp32 master and moments (row shards concatenated in rank order), plus the replicated small-tensor optimizer's
+        state.  Other ranks return an empty ``state``.  ``load_state_dict`` re-slices by rows, so the file resumes at
+        any world size that divides the row counts."""
         m = self.model
-        return {"step": m.step_count, "rank": m.comm.rank,
-                "state": {sw.name: {"master": sw.master.cpu(),
-                                    **({"exp_avg": sw.m.cpu()} if sw.m is not None else {}),
-                                    **({"exp_avg_sq": sw.v.cpu()} if sw.v is not None else {})}
-                          for sw in m.weights.values()}}
+        full: Dict[str, Dict[str, torch.Tensor]] = {}
+        for sw in m.weights.values():
+            for key, t in (("master", sw.master), ("exp_avg", sw.m), ("exp_avg_sq", sw.v)):
+                if t is None:
+                    continue
+                parts = m.comm.gather_to_root(t)
+                if parts is not None:
+                    full.setdefault(sw.name, {})[key] = torch.cat(parts, dim=0)
+        small = m.small_optimizer.state_dict() if (m.small_optimizer is not None and m.comm.rank == 0) else None
+        return {"step": m.step_count, "format": "full", "world_size": m.comm.world_size, "state": full, "small": small}
 
     def load_state_dict(self, sd: Dict[str, Any]) -> None:
+        """Every rank loads the same full-state dict and keeps its own rows."""
+        if sd.get("format") != "full":
+            raise ValueError("sharded optimizer state must be a full-state dict written by "
+                             "NativeShardedOptimizer.state_dict (per-rank shard dumps cannot be re-sharded)")
         m = self.model
         m.step_count = int(sd["step"])
+        r = m.comm.rank
         by_name = {sw.name: sw for sw in m.weights.values()}
         for name, st in sd["state"].items():
             sw = by_name[name]
-            sw.master.copy_(st["master"])
+            rows = slice(r * sw.rows_per_rank, (r + 1) * sw.rows_per_rank)
+            sw.master.copy_(st["master"][rows])
             if sw.m is not None and "exp_avg" in st:
-                sw.m.copy_(st["exp_avg"])
+                sw.m.copy_(st["exp_avg"][rows])
             if sw.v is not None and "exp_avg_sq" in st:
-                sw.v.copy_(st["exp_avg_sq"])
+                sw.v.copy_(st["exp_avg_sq"][rows])
+        if sd.get("small") is not None and m.small_optimizer is not None:
+            m.small_optimizer.load_state_dict(sd["small"])

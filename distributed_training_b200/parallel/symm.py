@@ -390,9 +390,20 @@ class SymmComm(Communicator):
         return self.stream
 
     def broadcast_(self, tensors: Sequence[torch.Tensor], src: int = 0) -> None:
+        """Tensors that already live in the heap (parameters re-homed next to their gradient buckets) are broadcast
+        IN PLACE, one kernel per tensor and no staging; anything else is coalesced into heap slabs, one peer-store
+        (or multimem.st) kernel per slab, and copied back."""
         if self.world_size == 1:
             return
-        # coalesce into heap slabs, one peer-store kernel per slab
+        staged: List[torch.Tensor] = []
+        for t in tensors:
+            if t.is_contiguous() and self.in_heap(t) and t.data_ptr() % 16 == 0:
+                seg, off = self.locate(t)
+                nbytes = (t.numel() * t.element_size() + 15) // 16 * 16     # heap slots are padded to 256 B
+                native.comm_broadcast(seg.desc, off, nbytes, src, self.comm_ctas)
+            else:
+                staged.append(t)
+        # coalesce the rest into heap slabs, one kernel per slab
         slab_cap = 256 << 20
         group: List[torch.Tensor] = []
         size = 0
@@ -419,7 +430,7 @@ class SymmComm(Communicator):
                         t.copy_(view)
             group, size = [], 0
 
-        for t in tensors:
+        for t in staged:
             nb = (t.numel() * t.element_size() + 15) // 16 * 16
             if size + nb > slab_cap:
                 flush()

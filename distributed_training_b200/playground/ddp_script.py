@@ -116,14 +116,10 @@ class FlatGradients:
 
 
 def average_gradients(model: nn.Module, comm: Communicator, flat: FlatGradients, per_param: bool) -> None:
-    if per_param:   # the reference's message pattern: one collective per parameter
-        for p in model.parameters():
-            buf = comm.alloc(p.numel(), p.dtype) if comm.device.type == "cuda" else p.grad.view(-1)
-            if buf.data_ptr() != p.grad.data_ptr():
-                buf.copy_(p.grad.view(-1))
-            comm.all_reduce_avg_(buf).wait()
-            if buf.data_ptr() != p.grad.data_ptr():
-                p.grad.view(-1).copy_(buf)
+    if per_param:   # the reference's message pattern: one collective per parameter, on that parameter's slice of
+        flat.reattach()    # the flat buffer (allocated once; nothing is taken from the symmetric heap per step)
+        for view in flat.views:
+            comm.all_reduce_avg_(view.view(-1)).wait()
         return
     flat.reattach()
     comm.all_reduce_avg_(flat.flat).wait()
@@ -146,7 +142,8 @@ def train(rank: int, world_size: int, args: argparse.Namespace) -> None:
 
         dataset = DummyDataset()
         sampler = ShardedSampler(dataset, num_replicas=world_size, rank=rank)
-        loader = ShardedLoader(dataset, args.batch_size, sampler=sampler, device=device)
+        loader = ShardedLoader(dataset, args.batch_size, sampler=sampler, device=device,
+                               num_workers=args.num_workers)
         optimizer = torch.optim.SGD(model.parameters(), lr=args.learning_rate)
         criterion = nn.MSELoss()
         flat = FlatGradients(list(model.parameters()), comm)

@@ -283,6 +283,15 @@ class Trainer:
             targets = targets.to(device, non_blocking=True)
         return self._run_batch(source, targets)
 
+    def check_comm_errors(self) -> None:
+        """Raise if a collective's spin watchdog fired (a peer never arrived): the kernels abandon the payload and
+        record the missing peer; this turns that record into an exception inside ``run()``'s try/except/finally
+        (SURVEY §5.3).  Called every ``log_every`` steps, before every snapshot and at the end of every epoch."""
+        comm = getattr(self._strategy, "comm", None)
+        check = getattr(comm, "check_errors", None)
+        if check is not None:
+            check()
+
     def _exposed_comm_ms(self) -> float:
         fn = getattr(self.model, "exposed_comm_ms", None)
         return float(fn()) if fn is not None else 0.0
@@ -300,11 +309,15 @@ class Trainer:
                 targets = targets.to(device, non_blocking=True)
             loss = self._run_batch(source, targets)
             self.metrics.update(loss, self._exposed_comm_ms, epoch)
+            if self.metrics.global_step % self.metrics.log_every == 0:
+                self.check_comm_errors()
+        self.check_comm_errors()
 
     def train(self, max_epochs: int) -> None:
         for epoch in range(self.epochs_run, max_epochs):
             self._run_epoch(epoch)
             if epoch % self.config.save_every == 0:
+                self.check_comm_errors()          # never write a snapshot of a run whose reductions were abandoned
                 self.checkpoint.save(self.model, epoch, self.optimizer if self.config.save_optimizer else None)
             self.epochs_run = epoch
 
@@ -372,9 +385,14 @@ def load_train_objs(cfg: Any) -> Tuple[Any, torch.nn.Module, Union[torch.optim.O
 
 
 def prepare_dataloader(dataset: Any, batch_size: int, device: Optional[torch.device] = None,
-                       seed: int = 0) -> ShardedLoader:
-    """Rank-sharded loader (``DistributedSampler`` semantics, shuffle on)."""
-    return ShardedLoader(dataset, batch_size, sampler=ShardedSampler(dataset, seed=seed), device=device)
+                       seed: int = 0, num_workers: int = 0) -> ShardedLoader:
+    """Rank-sharded loader (``DistributedSampler`` semantics, shuffle on).
+
+    With a CUDA ``device`` the loader stages batches in pinned memory and copies them on a side stream ahead of
+    the consumer (the reference: ``DataLoader(pin_memory=True)`` + blocking ``.to(device)``,
+    /root/reference/src/distributed_trainer.py:176-183,204-211); ``num_workers`` background threads do the gather."""
+    return ShardedLoader(dataset, batch_size, sampler=ShardedSampler(dataset, seed=seed), device=device,
+                         num_workers=num_workers)
 
 
 def setup_logging(cfg: Any) -> None:
@@ -421,7 +439,10 @@ def run(cfg: Any, before_teardown: Optional[Callable[["Trainer"], None]] = None)
         env = DistributedEnvironment(train_config.device)
         env.setup()
         dataset, model, optimizer = load_train_objs(cfg)
-        train_data = prepare_dataloader(dataset, train_config.batch_size, seed=train_config.seed)
+        # on a GPU the loader owns the H2D pipeline (pinned staging ring, copy stream, worker threads)
+        train_data = prepare_dataloader(dataset, train_config.batch_size,
+                                        device=env.torch_device if env.is_gpu else None, seed=train_config.seed,
+                                        num_workers=int(cfg.train.get("num_workers", 2 if env.is_gpu else 0)))
         trainer = Trainer(model, train_data, optimizer, train_config, env)
         trainer.train(train_config.max_epochs)
         if before_teardown is not None:

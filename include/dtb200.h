@@ -255,6 +255,8 @@ int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t shard_offset
 int dtb_debug_stream_probe(const void* a, const void* b, void* p, void* q, long long bytes, int ctas, void* stream);
 
 int dtb_comm_error_flag(const dtb_comm* c);
+/* Debug/benchmark only: cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault) on `stream` (peer-copy rate measurement). */
+int dtb_debug_memcpy_async(void* dst, const void* src, size_t bytes, void* stream);
 
 /* ---- host-side helpers for the symmetric heap --------------------------------- */
 /* CUDA IPC back end: cudaMalloc + cudaIpcGetMemHandle; handle_out must hold 64 bytes. Allocates device memory. */

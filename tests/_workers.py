@@ -130,6 +130,56 @@ def sharded_parity(rank, world, port, out_dir):
         dist.destroy_process_group()
 
 
+def sharded_optimizer_resume(rank, world, port, out_dir):
+    """fsdp + save_optimizer: a run that stops after 3 steps, is reloaded from the snapshot (model + optimizer state
+    written by rank 0) and continues must end, ON EVERY RANK, with the same master weights and moments as a run that
+    never stopped.  (Round 1 saved rank 0's shard only and loaded it into every rank.)"""
+    from distributed_training_b200.parallel.comm import TorchDistComm
+    from distributed_training_b200.parallel.sharded import FSDPStrategy
+    from distributed_training_b200.parallel.strategy import OptimizerSpec, atomic_torch_save
+
+    init(rank, world, port)
+    try:
+        def build(seed):
+            strategy = FSDPStrategy(is_gpu=False, comm=TorchDistComm(torch.device("cpu")))
+            model = strategy.prepare_model(make_mlp(seed + rank), "cpu")
+            return strategy, model, strategy.build_optimizer(model, OptimizerSpec("adamw", lr=0.01, weight_decay=0.1))
+
+        def steps(model, opt, lo, hi):
+            for step in range(lo, hi):
+                g = torch.Generator().manual_seed(50 + step)
+                xs, ys = torch.randn(world * 8, 20, generator=g), torch.randn(world * 8, 1, generator=g)
+                opt.zero_grad()
+                nn.functional.mse_loss(model(xs[rank * 8:(rank + 1) * 8]), ys[rank * 8:(rank + 1) * 8]).backward()
+                opt.step()
+
+        strategy, model, opt = build(400)
+        steps(model, opt, 0, 3)
+        snap = {"MODEL_STATE": model.state_dict(), "EPOCHS_RUN": 0, "OPTIMIZER_STATE": opt.state_dict()}  # collective
+        path = os.path.join(out_dir, "snap_opt.pt")
+        if rank == 0:
+            assert snap["OPTIMIZER_STATE"]["format"] == "full" and snap["OPTIMIZER_STATE"]["step"] == 3
+            for unit in model.units:       # rank 0 holds every rank's shard, not just its own
+                assert snap["OPTIMIZER_STATE"]["state"][unit.name]["exp_avg"].numel() == unit.full_numel
+            atomic_torch_save(snap, path)
+        dist.barrier()
+        steps(model, opt, 3, 5)                                    # the run that never stopped
+        want = {u.name: {k: v.clone() for k, v in opt.state[u.name].items()} for u in model.units}
+
+        strategy2, model2, opt2 = build(900)                       # "relaunch": different init, fresh optimizer
+        loaded = torch.load(path, weights_only=False)
+        strategy2.load_checkpoint(model2, loaded, "cpu")
+        opt2.load_state_dict(loaded["OPTIMIZER_STATE"])
+        assert opt2.step_count == 3
+        steps(model2, opt2, 3, 5)
+        for u in model2.units:
+            for k, v in opt2.state[u.name].items():
+                assert torch.equal(v, want[u.name][k]), (rank, u.name, k, (v - want[u.name][k]).abs().max())
+        torch.save({"ok": True}, os.path.join(out_dir, f"ok{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
 def mismatched_replicas(rank, world, port, out_dir):
     """Ranks wrap different architectures: the wrapper must refuse on EVERY rank (torch's shape verification)."""
     from distributed_training_b200.parallel.comm import TorchDistComm

@@ -27,6 +27,13 @@ def test_collectives_exact_and_bitwise_identical(tmp_path, nvls):
     assert res["nvls"] == (nvls == "1")
 
 
+@pytest.mark.timeout(120)
+def test_watchdog_turns_a_missing_peer_into_an_error(tmp_path):
+    w = 2
+    mp.spawn(G.watchdog, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
+    assert torch.load(tmp_path / "ok0.pt", weights_only=False)["raised"] is True
+
+
 def test_native_ddp_step_matches_single_process(tmp_path):
     w = _world()
     mp.spawn(G.ddp_native, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)

@@ -23,6 +23,27 @@ def test_sharded_strategy_matches_single_process(tmp_path):
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(2))
 
 
+def test_sharded_optimizer_state_resumes_on_every_rank(tmp_path):
+    mp.spawn(W.sharded_optimizer_resume, args=(2, free_port(), str(tmp_path)), nprocs=2, join=True)
+    assert all((tmp_path / f"ok{r}.pt").exists() for r in range(2))
+
+
+def test_fused_optimizer_state_dict_keeps_the_step_count():
+    from distributed_training_b200.optim import FusedAdamW
+
+    p = torch.nn.Parameter(torch.ones(4))
+    opt = FusedAdamW([p], lr=0.1, master_weights=False)
+    for _ in range(3):
+        p.grad = torch.ones(4)
+        opt.step()
+    sd = opt.state_dict()
+    assert sd["fused_step_count"] == 3
+    q = torch.nn.Parameter(torch.ones(4))
+    opt2 = FusedAdamW([q], lr=0.1, master_weights=False)
+    opt2.load_state_dict(sd)
+    assert opt2._step_count == 3 and torch.equal(opt2.state[q]["exp_avg"], opt.state[p]["exp_avg"])
+
+
 def _run_trainer(tmp_path, world, overrides, name):
     mp.spawn(W.trainer_run, args=(world, free_port(), str(tmp_path), overrides, name), nprocs=world, join=True)
     return [torch.load(tmp_path / f"{name}_rank{r}.pt", weights_only=False) for r in range(world)]
