@@ -91,12 +91,10 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
             for p in params:
                 grad_sink.mark_ready(p)
 
-    # a sharded grad_sink gathers each weight inside the first GEMM that consumes it
+    # a sharded grad_sink gathers each weight inside the forward GEMM that consumes it (gemm_forward) and hands out
+    # the transiently gathered matrix wherever else it is read (weight_view: embedding lookup, LM head, dgrad)
     gemm_fwd = getattr(grad_sink, "gemm_forward", None) or native.gemm
-    ensure = getattr(grad_sink, "ensure_gathered", None)
-    if ensure is not None:      # the embedding lookup reads the tables before any GEMM does
-        ensure(model.wte.weight)
-        ensure(model.wpe.weight)
+    wv = getattr(grad_sink, "weight_view", None) or (lambda p: p)
 
     def linear_fwd(x, lin: nn.Linear, out, *, act=0, d2=None, residual=None):
         out_f, in_f = lin.weight.shape
@@ -107,7 +105,7 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         """dx = dy W (optionally * gelu'(pre)); then dW = dy^T x_in, db = colsum(dy) into the buckets."""
         out_f, in_f = lin.weight.shape
         if dx_out is not None:
-            native.gemm(dy, lin.weight, dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
+            native.gemm(dy, wv(lin.weight), dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
                         act=2 if gelu_pre is not None else 0, max_ctas=max_ctas)
         native.gemm(dy, x_in, grad_of(lin.weight), m=out_f, n=in_f, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
         native.colsum_split(dy, grad_of(lin.bias))
@@ -119,7 +117,7 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         ready(ln.weight, ln.bias)
 
     # ------------------------------------------------------------------ forward
-    native.embedding_fwd(tokens, model.wte.weight, model.wpe.weight, ws["x0"])
+    native.embedding_fwd(tokens, wv(model.wte.weight), wv(model.wpe.weight), ws["x0"])
     x = ws["x0"]
     for blk, a in zip(model.h, ws["blocks"]):
         native.layernorm_fwd(x, None, blk.ln_1.weight, blk.ln_1.bias, a["a"], None, a["mean1"], a["rstd1"], eps)
@@ -132,7 +130,7 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         a["x_in"] = x
         x = a["x_out"]
     native.layernorm_fwd(x, None, model.ln_f.weight, model.ln_f.bias, ws["xf"], None, ws["meanf"], ws["rstdf"], eps)
-    native.gemm(ws["xf"], model.wte.weight, ws["logits"], m=R, n=V, k=C, max_ctas=max_ctas)
+    native.gemm(ws["xf"], wv(model.wte.weight), ws["logits"], m=R, n=V, k=C, max_ctas=max_ctas)
     native.cross_entropy_fwd_bwd(ws["logits"], targets, ws["row_loss"], cfg.vocab_size, 1.0 / R)
     native.mean_f32(ws["row_loss"], ws["loss"])
 
@@ -140,7 +138,7 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
     dlogits = ws["logits"]
     dxa, dxb = ws["dx"]
     # LM head (tied): dxf = dlogits wte ; dwte = dlogits^T xf  (embedding gradient is added at the very end)
-    native.gemm(dlogits, model.wte.weight, ws["dC"], m=R, n=C, k=V, b_mn=True, max_ctas=max_ctas)
+    native.gemm(dlogits, wv(model.wte.weight), ws["dC"], m=R, n=C, k=V, b_mn=True, max_ctas=max_ctas)
     native.gemm(dlogits, ws["xf"], grad_of(model.wte.weight), m=V, n=C, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
     ln_bwd(ws["dC"], x, model.ln_f, ws["meanf"], ws["rstdf"], None, dxa)
     dx = dxa                                   # gradient w.r.t. the block output

@@ -106,6 +106,7 @@ class MLP(nn.Module):
 
         # a sharded grad_sink gathers the weight inside the forward GEMM (all-gather -> GEMM fusion)
         gemm_fwd = getattr(grad_sink, "gemm_forward", None) or native.gemm
+        wv = getattr(grad_sink, "weight_view", None) or (lambda p: p)     # sharded: transiently re-gathered matrix
         # ---- forward: h_{i+1} = gelu(h_i W_i^T + b_i), pre-activation kept for backward
         h = x
         for i, layer in enumerate(self.layers):
@@ -132,7 +133,7 @@ class MLP(nn.Module):
                 # dgrad fused with GELU': dz_prev = (dz W_i) * gelu'(z_{i-1}).  It runs BEFORE this layer's
                 # wgrad is handed to the reducer: a fused reduce+SGD (or the fused epilogue below) overwrites W_i.
                 nxt = ws["dz"][i % 2]
-                native.gemm(dz, layer.weight, nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
+                native.gemm(dz, wv(layer.weight), nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
                             ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=cap)
             if fused_sgd is not None:
                 # single replica: W = (1 - lr*wd) W - lr * (dz^T h_in), applied in the wgrad epilogue (no dW in HBM)

@@ -352,6 +352,29 @@ def sharded_native(rank, world, port, out_dir):
                 ropt.zero_grad()
                 rloss.backward()
                 ropt.step()
+            # ---- FULL_SHARD bookkeeping: full matrices only live in the pools, and the all-gather that runs INSIDE
+            # the forward GEMM reproduces every rank's shard bit for bit
+            if kind.startswith("mlp"):
+                persistent = sum(sw.shard.numel() for sw in wrapped.weights.values())
+                total = sum(sw.rows * sw.cols for sw in wrapped.weights.values())
+                assert persistent * world == total
+                assert all(sw.param.data.untyped_storage().nbytes() <= 4 for sw in wrapped.weights.values())
+                lin = model.layers[1]
+                sw = wrapped.weights[id(lin.weight)]
+                if sw.full_slot is not None:
+                    sw.full_slot.owner, sw.full_slot = None, None           # force the fused gather
+                xin = torch.randn(256, lin.weight.shape[1], device="cuda").to(torch.bfloat16)
+                out = torch.empty(256, lin.weight.shape[0], device="cuda", dtype=torch.bfloat16)
+                wrapped.gemm_forward(xin, lin.weight, out, m=256, n=lin.weight.shape[0], k=lin.weight.shape[1])
+                torch.cuda.synchronize()
+                shards = _gather_cpu(sw.shard.contiguous(), world)
+                assert torch.equal(sw.full.cpu(), torch.cat(shards, dim=0)), "fused gather is not bit-exact"
+                ref_out = xin.float() @ torch.cat(shards, dim=0).float().cuda().t()
+                assert torch.allclose(out.float(), ref_out, atol=2e-2, rtol=2e-2)
+                # the stand-alone (backward) gather gives the same bytes
+                sw.full_slot.owner, sw.full_slot = None, None
+                assert torch.equal(wrapped.weight_view(lin.weight).cpu(), torch.cat(shards, dim=0))
+                wrapped._access = []
             full = wrapped.state_dict()                      # collective gather of every shard
             tol = 3e-2 if kind.endswith("sgd") else 2e-2
             for k, v in ref.state_dict().items():
