@@ -35,6 +35,22 @@ class PooledClassificationDataset(Dataset):
         return self.x[j], self.y[j]
 
 
+class TokenPairDataset(Dataset):
+    """Synthetic next-token pairs: ``size`` sequences of ``seq_len`` tokens, targets = inputs shifted by one."""
+
+    def __init__(self, size: int, seq_len: int = 1024, vocab: int = 50257, seed: int = 0):
+        g = torch.Generator().manual_seed(seed)
+        stream = torch.randint(0, vocab, (size, seq_len + 1), generator=g, dtype=torch.int64)
+        self.x = stream[:, :-1].contiguous()
+        self.y = stream[:, 1:].contiguous()
+
+    def __len__(self) -> int:
+        return int(self.x.shape[0])
+
+    def __getitem__(self, i: int):
+        return self.x[i], self.y[i]
+
+
 class _TorchBlock(nn.Module):
     def __init__(self, c: int, heads: int, dtype: torch.dtype) -> None:
         super().__init__()

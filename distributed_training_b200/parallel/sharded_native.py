@@ -122,8 +122,6 @@ class NativeShardedModule(nn.Module):
         self.reshard_after_forward = reshard_after_forward
         self.prefetch_ahead = max(int(prefetch_ahead), 0)
         w = comm.world_size
-        comm.broadcast_([p.data for p in module.parameters()] + [b.data for b in module.buffers()], src=0)
-
         named = list(module.named_parameters())
         big = [(n, p) for n, p in named if self._shardable(p, w)]
         small = [(n, p) for n, p in named if not self._shardable(p, w)]
@@ -137,7 +135,12 @@ class NativeShardedModule(nn.Module):
         need = sum(p.numel() * 2 // w + 512 for _, p in big)
         need += sum(2 * d * (numel * 2 + 512) for numel, d in depth.items())
         need += sum(p.numel() * 2 + 512 for _, p in small) + (1 << 20)
-        segment = comm.reserve(need)
+        # the init broadcast's staging slab comes out of the same segment (reserved first, so nothing else is mapped)
+        staging = min(256 << 20, sum(p.numel() * p.element_size() for p in module.parameters()) + (1 << 20))
+        segment = comm.reserve(need + (staging if w > 1 else 0) + (1 << 20))
+        comm.broadcast_([p.data for p in module.parameters()] + [b.data for b in module.buffers()], src=0)
+        if segment.nbytes - segment.used < need:
+            segment = comm.reserve(need)
         self.segment = segment
         self.weights: "OrderedDict[int, _ShardedWeight]" = OrderedDict()
         for n, p in big:

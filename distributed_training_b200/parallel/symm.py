@@ -369,7 +369,7 @@ class SymmComm(Communicator):
     def scratch(self, nbytes: int) -> torch.Tensor:
         """A reusable heap buffer for operands that were not allocated in the heap."""
         if self._scratch is None or self._scratch.numel() < nbytes:
-            self._scratch = self.alloc(max(nbytes, 64 << 20), torch.uint8)
+            self._scratch = self.alloc(max(nbytes, 1 << 20), torch.uint8)
         return self._scratch[:nbytes]
 
     # ------------------------------------------------------------ collectives
@@ -405,6 +405,8 @@ class SymmComm(Communicator):
                 staged.append(t)
         # coalesce the rest into heap slabs, one kernel per slab
         slab_cap = 256 << 20
+        if staged:      # size the staging buffer once (scratch() never shrinks or frees)
+            self.scratch(min(slab_cap, sum((t.numel() * t.element_size() + 15) // 16 * 16 for t in staged)))
         group: List[torch.Tensor] = []
         size = 0
 

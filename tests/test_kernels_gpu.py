@@ -44,6 +44,48 @@ def test_gemm_layouts_and_tiles(a_mn, b_mn, cta_pair, tile_n, m, n, k):
     assert torch.allclose(out.float(), ref, atol=0.25, rtol=2e-2)
 
 
+def _gemm_ref_bf16_inputs(a, b, a_mn, b_mn):
+    """fp32 oracle computed on the GPU in chunks (the north-star shapes are too large for one fp32 matmul on a
+    shared box to be cheap on the host; TF32 is disabled so the oracle is true fp32)."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        return _gemm_ref(a, b, a_mn, b_mn)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+
+
+# The shapes the benchmarks actually run (SURVEY §4.3: "on the north-star shapes"): the wide MLP's 8192-class GEMMs in
+# all four operand layouts, GPT-2 XL's fc forward (K = 1600: 25 k-blocks, N tail), its fc-proj wgrad (K = 4096 rows),
+# the short-K family of GPT-2 small, and the LM head over the padded vocabulary at K = 768.
+NORTH_STAR = [
+    # m, n, k, a_mn, b_mn
+    (4096, 8192, 8192, False, False),      # wide MLP forward
+    (4096, 8192, 8192, False, True),       # dgrad
+    (8192, 8192, 4096, True, True),        # wgrad
+    (8192, 8192, 8192, True, False),       # the fourth layout at the 8192 class
+    (4096, 6400, 1600, False, False),      # GPT-2 XL fc forward
+    (4096, 1600, 6400, False, True),       # GPT-2 XL fc dgrad
+    (6400, 1600, 4096, True, True),        # GPT-2 XL fc wgrad
+    (8192, 2304, 768, False, False),       # GPT-2 small qkv forward
+    (8192, 50304, 768, False, False),      # LM head forward
+    (8192, 768, 50304, False, True),       # LM head dgrad
+]
+
+
+@pytest.mark.parametrize("m,n,k,a_mn,b_mn", NORTH_STAR)
+def test_gemm_north_star_shapes(m, n, k, a_mn, b_mn):
+    a = _bf16(*((k, m) if a_mn else (m, k)), seed=21)
+    b = _bf16(*((k, n) if b_mn else (n, k)), scale=1.0 / math.sqrt(k), seed=22)
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    native.gemm(a, b, out, m=m, n=n, k=k, a_mn=a_mn, b_mn=b_mn)
+    ref = _gemm_ref_bf16_inputs(a, b, a_mn, b_mn)
+    torch.cuda.synchronize()
+    # outputs are O(1); bf16 rounding of the result dominates (2^-8 relative), accumulation is fp32 in TMEM
+    assert torch.allclose(out.float(), ref, atol=2e-2, rtol=1e-2), (out.float() - ref).abs().max().item()
+    del ref
+
+
 def test_gemm_bias_gelu_epilogue_and_preactivation():
     m, n, k = 512, 1024, 512
     x, w = _bf16(m, k, seed=3), _bf16(n, k, scale=0.05, seed=4)
@@ -337,7 +379,7 @@ def _attn_ref(qkv, heads):
     return o.transpose(1, 2).reshape(B, T, C), lse
 
 
-@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 3), (2, 1024, 12)])
+@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 3), (2, 1024, 12), (4, 1024, 25)])
 def test_attention_fwd(B, T, H):
     qkv = _bf16(B, T, 3 * H * 64, seed=1)
     out = torch.empty(B, T, H * 64, dtype=torch.bfloat16, device=DEV)
@@ -348,7 +390,7 @@ def test_attention_fwd(B, T, H):
     assert torch.allclose(out.float(), ref, atol=3e-2, rtol=3e-2)
 
 
-@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 384, 2), (1, 1024, 4)])
+@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 384, 2), (1, 1024, 4), (4, 1024, 25), (8, 1024, 12)])
 def test_attention_bwd(B, T, H):
     qkv = _bf16(B, T, 3 * H * 64, seed=2)
     dout = _bf16(B, T, H * 64, seed=3)
