@@ -26,6 +26,7 @@ peer-memory kernels on B200 (``SymmComm``).
 from __future__ import annotations
 
 import contextlib
+import os
 import zlib
 import logging
 import time
@@ -258,6 +259,8 @@ class ReplicatedModule(nn.Module):
 
     #: weights smaller than this are reduced in one piece even when they end backward
     TAIL_CHUNK_MIN_BYTES = 32 << 20
+    #: pieces the last weight gradient of backward is produced (and reduced) in; DTB_DDP_TAIL_CHUNKS overrides
+    TAIL_CHUNKS = int(os.environ.get("DTB_DDP_TAIL_CHUNKS", "4"))
 
     def tail_chunks(self, param: nn.Parameter) -> int:
         """How many row chunks the *last* weight gradient of backward should be produced in.  Its reduction
@@ -267,7 +270,7 @@ class ReplicatedModule(nn.Module):
         bucket = self._bucket_of[i]
         if self.comm.world_size == 1 or bucket.expected != 1 or param.dim() != 2 or param.shape[0] % 4:
             return 1
-        return 4 if bucket.plan.nbytes >= self.TAIL_CHUNK_MIN_BYTES else 1
+        return self.TAIL_CHUNKS if bucket.plan.nbytes >= self.TAIL_CHUNK_MIN_BYTES else 1
 
     def mark_ready_chunk(self, param: nn.Parameter, chunk: int, n_chunks: int) -> None:
         """Rows ``[chunk, chunk+1) * rows/n_chunks`` of ``param``'s gradient are final: reduce just that slice
