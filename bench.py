@@ -195,7 +195,15 @@ def run_ours(args):
     if args.comm_exclusive >= 0 and comm is not None and hasattr(comm, "exclusive_sms"):
         comm.exclusive_sms = args.comm_exclusive
     assert trainer.model.native_step, "the native tcgen05 path must be the one that runs"
+    mem_trace = os.environ.get("DTB_MEM_TRACE", "0") == "1" and rank == 0
 
+    def mem(tag):
+        if mem_trace:
+            print(f"[mem] {tag}: allocated {torch.cuda.memory_allocated() / 2**30:.2f} GB, peak "
+                  f"{torch.cuda.max_memory_allocated() / 2**30:.2f} GB, heap {heap_bytes(comm) / 2**30:.2f} GB",
+                  file=sys.stderr, flush=True)
+
+    mem("after trainer construction")
     dev_pool = device_pool(args, device, seed=1000 + rank)
 
     def step_dev(i):
@@ -205,6 +213,18 @@ def run_ours(args):
     with ClockSampler(local_rank) as sampler:
         for i in range(args.warmup):
             step_dev(i)
+            if i == 0:
+                torch.cuda.synchronize()
+                mem("after first step")
+                if mem_trace:      # the largest live blocks, by size
+                    sizes = {}
+                    for seg in torch.cuda.memory_snapshot():
+                        for blk in seg["blocks"]:
+                            if blk["state"] == "active_allocated":
+                                sizes[blk["size"]] = sizes.get(blk["size"], 0) + 1
+                    top = sorted(sizes.items(), key=lambda kv: -kv[0] * kv[1])[:12]
+                    print("[mem] live blocks (MiB x count): " + ", ".join(f"{k / 2**20:.1f}x{v}" for k, v in top),
+                          file=sys.stderr, flush=True)
         torch.cuda.synchronize()
         native.reset_launch_count()
         sampler.mark_start()
@@ -239,17 +259,22 @@ def run_ours(args):
     loader = prepare_dataloader(dataset, args.batch, device=device, seed=0, num_workers=args.loader_workers)
     trainer.train_data = loader
     loader.sampler.set_epoch(0)
-    timed, h2d = 0, 0
+    timed, h2d, waited = 0, 0, 0.0
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    for i, (source, targets) in enumerate(trainer.train_data):
+    it = iter(trainer.train_data)
+    for i in range(e2e_steps):
         if i == e2e_warm:
             barrier_sync()
             start.record()
+        t0 = time.perf_counter()
+        source, targets = next(it)                   # host time spent waiting for the loader (diagnostic)
+        waited += (time.perf_counter() - t0) if i >= e2e_warm else 0.0
         h2d = source.numel() * source.element_size() + targets.numel() * targets.element_size()
         loss = trainer._run_batch(source, targets)
         loss.item()
         timed += int(i >= e2e_warm)
     stop.record()
+    loader_wait_ms = waited / max(timed, 1) * 1e3
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks(start.elapsed_time(stop))
     barrier_sync()
@@ -267,8 +292,12 @@ def run_ours(args):
                                   "comm": {"heap": getattr(comm, "backend", None),
                                            "nvls": bool(getattr(comm, "nvls_active", False)),
                                            "exclusive_sms": getattr(comm, "exclusive_sms", 0)},
-                                  "e2e_path": "dataset -> ShardedSampler -> ShardedLoader(pinned, "
-                                              f"{args.loader_workers} worker threads) -> Trainer._run_batch -> loss.item()"})
+                                  "e2e_path": "dataset -> ShardedSampler -> ShardedLoader("
+                                              + ("rows pulled from the pinned dataset by dtb_gather_rows on the copy "
+                                                 "stream" if loader.device_gather else
+                                                 f"pinned staging, {args.loader_workers} worker threads")
+                                              + ") -> Trainer._run_batch -> loss.item()",
+                                  "loader_wait_ms_per_step": loader_wait_ms, "host_cpus": os.cpu_count()})
         print(json.dumps(line), flush=True)
     if comm is not None:
         comm.close()

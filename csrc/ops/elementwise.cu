@@ -332,3 +332,64 @@ extern "C" int dtb_mean_f32(const float* x, long long n, float* out, void* strea
   DTB_LAUNCH_OK();
   return 0;
 }
+
+// ---- row gather (input pipeline) ---------------------------------------------------------------------------------
+// dst[i, :] = src[idx[i], :] for `rows` rows of `row_bytes` bytes.  `src` may be PINNED HOST memory (device-accessible
+// under unified addressing): the batch is then assembled by the GPU pulling exactly the sampled rows over PCIe, with no
+// host-side memcpy into a staging buffer at all.  This is the H2D leg of the reference's DataLoader(pin_memory=True) +
+// .to(device) (/root/reference/src/distributed_trainer.py:176-183,204-211) done as one kernel on the copy stream.
+// A handful of CTAs is enough: the transfer is PCIe-bound (~55 GB/s), not SM-bound.
+namespace dtb {
+namespace gather {
+
+template <typename V>
+__global__ void __launch_bounds__(256, 4)
+gather_rows_kernel(const uint8_t* __restrict__ src, const long long* __restrict__ idx, uint8_t* __restrict__ dst, int rows,
+                   long long row_vecs, long long src_rows) {
+  const long long total = static_cast<long long>(rows) * row_vecs;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total; i0 += stride * 4) {
+    V val[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < total) {
+        const long long r = i / row_vecs, c = i - r * row_vecs;
+        long long s = idx[r];
+        if (src_rows > 0) s %= src_rows;
+        val[u] = *reinterpret_cast<const V*>(src + (s * row_vecs + c) * sizeof(V));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < total) *reinterpret_cast<V*>(dst + i * sizeof(V)) = val[u];
+    }
+  }
+}
+
+}  // namespace gather
+}  // namespace dtb
+
+extern "C" int dtb_gather_rows(const void* src, const long long* idx, void* dst, int rows, long long row_bytes,
+                               long long src_rows, int max_ctas, void* stream) {
+  DTB_REQUIRE(src && idx && dst && rows >= 0 && row_bytes > 0 && row_bytes % 4 == 0,
+              "dtb_gather_rows: row_bytes=%lld must be a positive multiple of 4", row_bytes);
+  if (rows == 0) return 0;
+  auto s = static_cast<cudaStream_t>(stream);
+  auto S = static_cast<const uint8_t*>(src);
+  auto D = static_cast<uint8_t*>(dst);
+  const bool a16 = row_bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) % 16 == 0;
+  const bool a8 = row_bytes % 8 == 0 && (reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) % 8 == 0;
+  const long long vec = a16 ? 16 : (a8 ? 8 : 4);
+  const long long total = static_cast<long long>(rows) * (row_bytes / vec);
+  long long need = (total + 256 * 4 - 1) / (256 * 4);
+  const int cap = max_ctas > 0 ? max_ctas : 16;
+  const int grid = static_cast<int>(need < cap ? (need < 1 ? 1 : need) : cap);
+  using namespace dtb::gather;
+  if (a16) gather_rows_kernel<uint4><<<grid, 256, 0, s>>>(S, idx, D, rows, row_bytes / 16, src_rows);
+  else if (a8) gather_rows_kernel<uint2><<<grid, 256, 0, s>>>(S, idx, D, rows, row_bytes / 8, src_rows);
+  else gather_rows_kernel<uint32_t><<<grid, 256, 0, s>>>(S, idx, D, rows, row_bytes / 4, src_rows);
+  DTB_LAUNCH_OK();
+  return 0;
+}

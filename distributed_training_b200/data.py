@@ -178,6 +178,15 @@ class ShardedSampler(Sampler[int]):
         return self.num_samples
 
 
+def _native_available() -> bool:
+    try:
+        from .ops import native
+
+        return native.available()
+    except Exception:  # pragma: no cover
+        return False
+
+
 class ShardedLoader:
     """Batch iterator over a :class:`TensorPairDataset` shard.
 
@@ -187,11 +196,18 @@ class ShardedLoader:
     buffer).  ``num_workers > 0``: that many background threads gather and copy up to ``prefetch`` batches ahead, so
     a 67 MB/step input stream (wide-MLP config) costs the training thread nothing.
     ``device=None`` yields CPU batches (the ``Trainer`` moves them).
+
+    ``device_gather`` (default on a B200 when the dataset exposes dense ``tensors()``): the dataset's tensors are
+    pinned ONCE and every batch is assembled by a kernel on the copy stream that pulls exactly the sampled rows out
+    of pinned host memory over PCIe (``dtb_gather_rows``) -- no host-side staging copy, no worker threads; the host
+    only ships the batch's indices.  Eight ranks x 67 MB/step of ``index_select`` on one host made the end-to-end
+    step 1.3-1.9 ms slower than the device-timed one; the kernel-side gather removes that host work.
     """
 
     def __init__(self, dataset: Dataset, batch_size: int, sampler: Optional[ShardedSampler] = None,
                  device: Optional[torch.device] = None, drop_last: bool = False,
-                 pin_memory: Optional[bool] = None, num_workers: int = 0, prefetch: int = 3) -> None:
+                 pin_memory: Optional[bool] = None, num_workers: int = 0, prefetch: int = 3,
+                 device_gather: Optional[bool] = None) -> None:
         self.dataset = dataset
         self.batch_size = int(batch_size)
         self.sampler = sampler if sampler is not None else ShardedSampler(dataset, 1, 0, shuffle=False)
@@ -204,6 +220,12 @@ class ShardedLoader:
         self._copy_stream = torch.cuda.Stream(self.device) if cuda else None
         self._staging: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None] * (self.prefetch + 1 if self.num_workers else 2)
         self._pool: Optional[ThreadPoolExecutor] = None
+        if device_gather is None:
+            device_gather = cuda and hasattr(dataset, "tensors") and _native_available()
+        self.device_gather = bool(device_gather) and cuda
+        self._pinned_data: Optional[Tuple[torch.Tensor, torch.Tensor]] = None
+        self._idx_staging: List[Optional[torch.Tensor]] = [None, None]
+        self._idx_events: List[Optional["torch.cuda.Event"]] = [None, None]
 
     def __len__(self) -> int:
         n = len(self.sampler)
@@ -247,7 +269,53 @@ class ShardedLoader:
             chunks.pop()
         return chunks
 
+    # ---- device-side gather from pinned host memory -----------------------------------------------------------
+    def _pinned_dataset(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self._pinned_data is None:
+            xs, ys = self.dataset.tensors()  # type: ignore[attr-defined]
+            self._pinned_data = (xs if xs.is_pinned() else xs.contiguous().pin_memory(),
+                                 ys if ys.is_pinned() else ys.contiguous().pin_memory())
+        return self._pinned_data
+
+    def _issue_device_gather(self, idx: torch.Tensor, slot: int):
+        from .ops import native
+
+        xs, ys = self._pinned_dataset()
+        if hasattr(self.dataset, "remap"):
+            idx = self.dataset.remap(idx)  # type: ignore[attr-defined]
+        n = int(idx.numel())
+        if self._idx_staging[slot] is None:
+            self._idx_staging[slot] = torch.empty(self.batch_size, dtype=torch.int64).pin_memory()
+        elif self._idx_events[slot] is not None:
+            self._idx_events[slot].synchronize()          # issued two batches ago: long done
+        stage = self._idx_staging[slot][:n]
+        stage.copy_(idx)
+        cs = self._copy_stream
+        with torch.cuda.stream(cs):
+            idx_dev = stage.to(self.device, non_blocking=True)
+            out_x = torch.empty((n, *xs.shape[1:]), dtype=xs.dtype, device=self.device)
+            out_y = torch.empty((n, *ys.shape[1:]), dtype=ys.dtype, device=self.device)
+            native.gather_rows(xs, idx_dev, out_x, stream=cs.cuda_stream)
+            native.gather_rows(ys, idx_dev, out_y, stream=cs.cuda_stream)
+            event = torch.cuda.Event()
+            event.record(cs)
+        self._idx_events[slot] = event
+        return (out_x, out_y), event
+
+    def _iter_device_gather(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        pending = None
+        for i, idx in enumerate(self._chunks()):
+            nxt = self._issue_device_gather(idx, i % 2)
+            if pending is not None:
+                yield self._release(pending)
+            pending = nxt
+        if pending is not None:
+            yield self._release(pending)
+
     def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        if self.device_gather:
+            yield from self._iter_device_gather()
+            return
         if self.num_workers > 0:
             yield from self._iter_threaded()
             return

@@ -295,6 +295,18 @@ def cast_bf16_to_f32(src, dst):
     return dst
 
 
+def gather_rows(src: torch.Tensor, idx: torch.Tensor, dst: torch.Tensor, src_rows: int = 0, max_ctas: int = 0,
+                stream: Optional[int] = None) -> torch.Tensor:
+    """``dst[i] = src[idx[i] % src_rows]`` (rows of the first dimension); ``src`` may be a PINNED host tensor, which
+    the kernel reads over PCIe.  ``idx`` (int64) and ``dst`` live on the device."""
+    assert idx.dtype == torch.int64 and idx.is_cuda and dst.is_cuda and src.is_contiguous() and dst.is_contiguous()
+    assert src.is_cuda or src.is_pinned(), "gather_rows: host sources must be pinned"
+    row_bytes = (src.numel() // max(src.shape[0], 1)) * src.element_size()
+    _ok(lib().dtb_gather_rows(_p(src), _p(idx), _p(dst), int(idx.numel()), C.c_longlong(row_bytes),
+                              C.c_longlong(src_rows), max_ctas, _stream(stream)))
+    return dst
+
+
 def sumsq(x, out):
     _ok(lib().dtb_sumsq(_p(x), int(x.dtype == torch.float32), C.c_longlong(x.numel()), _p(out), _stream()))
     return out

@@ -260,7 +260,7 @@ class ReplicatedModule(nn.Module):
     #: weights smaller than this are reduced in one piece even when they end backward
     TAIL_CHUNK_MIN_BYTES = 32 << 20
     #: pieces the last weight gradient of backward is produced (and reduced) in; DTB_DDP_TAIL_CHUNKS overrides
-    TAIL_CHUNKS = int(os.environ.get("DTB_DDP_TAIL_CHUNKS", "4"))
+    TAIL_CHUNKS = int(os.environ.get("DTB_DDP_TAIL_CHUNKS", "8"))
 
     def tail_chunks(self, param: nn.Parameter) -> int:
         """How many row chunks the *last* weight gradient of backward should be produced in.  Its reduction
@@ -268,7 +268,7 @@ class ReplicatedModule(nn.Module):
         remaining wgrad GEMMs."""
         i = self._index_of[id(param)]
         bucket = self._bucket_of[i]
-        if self.comm.world_size == 1 or bucket.expected != 1 or param.dim() != 2 or param.shape[0] % 4:
+        if self.comm.world_size == 1 or bucket.expected != 1 or param.dim() != 2 or param.shape[0] % self.TAIL_CHUNKS:
             return 1
         return self.TAIL_CHUNKS if bucket.plan.nbytes >= self.TAIL_CHUNK_MIN_BYTES else 1
 

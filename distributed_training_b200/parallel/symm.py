@@ -150,9 +150,14 @@ class SymmComm(Communicator):
         self.comm_ctas = comm_ctas if comm_ctas else (128 if self.world_size == 2 else 0)
         #: > 0: while a native step whose backward GEMMs leave that many SMs free is running (ReplicatedModule sets
         #: ``exclusive_now``), large bf16 all-reduces run there on whole-SM CTAs (clusters of two) at their stand-alone
-        #: speed instead of sharing SMs with GEMM CTAs.  Measured at 4 GPUs: 10.33 ms/step vs 11.27 co-resident.
-        #: DTB_COMM_EXCLUSIVE_SMS overrides (0 = always co-resident).
-        self.exclusive_sms = int(os.environ.get("DTB_COMM_EXCLUSIVE_SMS", "16" if self.world_size > 1 else "0"))
+        #: speed instead of sharing SMs with GEMM CTAs.  DTB_COMM_EXCLUSIVE_SMS overrides (0 = always co-resident);
+        #: the default is resolved with the first segment (``_default_exclusive_sms``): the NVLS kernels issue one
+        #: multimem.ld_reduce + one multimem.st per 16 bytes, so 4 SMs carry the reduction at link rate and the GEMMs
+        #: keep 144 (8 GPUs, wide MLP: 10.22 ms/step with 4 SMs, 10.64 with 8, 10.79 with 16, 10.95 co-resident); the
+        #: peer-load kernels need 16 (4 GPUs, round 1: 10.33 ms vs 11.27 co-resident).
+        env_excl = os.environ.get("DTB_COMM_EXCLUSIVE_SMS")
+        self.exclusive_sms = int(env_excl) if env_excl is not None else (16 if self.world_size > 1 else 0)
+        self._exclusive_from_env = env_excl is not None
         self.exclusive_min_bytes = 8 << 20
         self.exclusive_now = False     # set by the data-parallel wrapper while a step that left SMs free is running
         #: opt-in (DTB_COMM_CE=1): large bf16 all-reduces move their NVLink legs with the copy engines
@@ -219,6 +224,8 @@ class SymmComm(Communicator):
         else:
             seg = self._new_segment_ipc(nbytes)
         self.segments.append(seg)
+        if len(self.segments) == 1 and not self._exclusive_from_env and self.nvls_active:
+            self.exclusive_sms = 4
         if self.world_size > 1:
             dist.barrier()     # every rank has mapped every peer before the first kernel touches it
         logger.info(f"[rank {self.rank}] symmetric segment {seg.index}: {seg.nbytes / 2**20:.0f} MiB mapped on "

@@ -112,6 +112,13 @@ int dtb_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
 /* sum of squares of n elements into *out (fp32, accumulated with atomicAdd; caller zeroes). K15. */
 int dtb_sumsq(const void* x, int is_fp32, long long n, float* out, void* stream);
 
+/* Input pipeline (K14: the H2D copy behind DataLoader(pin_memory=True) + .to(device),
+ * /root/reference/src/distributed_trainer.py:176-183): dst[i,:] = src[idx[i] (% src_rows if src_rows > 0), :] for
+ * `rows` rows of `row_bytes` bytes (multiple of 4).  `src` may be pinned HOST memory: the GPU then pulls exactly the
+ * sampled rows over PCIe and no host-side staging copy exists.  idx and dst are device memory.  max_ctas: 0 = 16. */
+int dtb_gather_rows(const void* src, const long long* idx, void* dst, int rows, long long row_bytes,
+                    long long src_rows, int max_ctas, void* stream);
+
 /* ---- LayerNorm (K16) ------------------------------------------------------- */
 /* y = LN(x [+ residual]) * gamma + beta; when residual != NULL, xres_out receives x + residual. */
 int dtb_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,

@@ -250,7 +250,7 @@ def ddp_native(rank, world, port, out_dir):
         assert wrapped.native_step
         if str(fused).endswith("chunked"):
             wrapped.TAIL_CHUNK_MIN_BYTES = 0
-            assert wrapped.tail_chunks(model.layers[0].weight) == 4
+            assert wrapped.tail_chunks(model.layers[0].weight) == wrapped.TAIL_CHUNKS
         spec = (OptimizerSpec("adamw", lr=2e-3, weight_decay=0.01) if adamw else
                 OptimizerSpec("sgd", lr=0.05, weight_decay=0.01))
         opt = strategy.build_optimizer(wrapped, spec)

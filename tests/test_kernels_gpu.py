@@ -211,7 +211,8 @@ def test_layernorm_fwd(rows, cols, with_res):
         assert torch.equal(xres, xin.to(torch.bfloat16))
 
 
-@pytest.mark.parametrize("rows,cols", [(2048, 768), (300, 1600)])
+@pytest.mark.parametrize("rows,cols", [(2048, 768), (300, 1600), (8192, 768), (4096, 1600), (513, 1024), (64, 2048),
+                                       (100, 72), (3, 512)])
 def test_layernorm_bwd(rows, cols):
     x, dy, dres = _bf16(rows, cols, seed=1), _bf16(rows, cols, seed=2), _bf16(rows, cols, seed=5)
     g, b = _bf16(cols, seed=3) * 0.1 + 1, _bf16(cols, seed=4) * 0.1

@@ -57,3 +57,23 @@ def test_native_sharded_module_spanning_small_segments():
     torch.cuda.synchronize()
     assert float(loss) < l0
     comm.close()
+
+
+def test_loader_device_gather_matches_host_gather():
+    """The kernel that assembles a batch straight out of pinned host memory (dtb_gather_rows on the copy stream)
+    yields exactly the batches of the host index_select + staged-copy path, ragged last batch included."""
+    from distributed_training_b200.data import PooledWideDataset, ShardedLoader, ShardedSampler, TokenDataset
+
+    dev = torch.device("cuda", 0)
+    for ds in (PooledWideDataset(1000, 264, 10, pool=128), TokenDataset(100, 33, 1000)):
+        host = ShardedLoader(ds, 32, sampler=ShardedSampler(ds, 2, 1, seed=3), device=dev, device_gather=False)
+        gpu = ShardedLoader(ds, 32, sampler=ShardedSampler(ds, 2, 1, seed=3), device=dev)
+        assert gpu.device_gather and not host.device_gather
+        a, b = list(host), list(gpu)
+        torch.cuda.synchronize()
+        assert len(a) == len(b) and a[-1][0].shape[0] < 32
+        for (xa, ya), (xb, yb) in zip(a, b):
+            assert xb.is_cuda and torch.equal(xa, xb) and torch.equal(ya, yb)
+        again = list(gpu)                                   # staging slots and events are reused across epochs
+        torch.cuda.synchronize()
+        assert all(torch.equal(p[0], q[0]) for p, q in zip(b, again))
