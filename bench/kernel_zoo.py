@@ -111,11 +111,15 @@ def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--ncu", action="store_true")
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--only", default="", help="comma-separated substrings: run only the kernels whose name matches one")
     ns = ap.parse_args()
     native.require()
     peaks = json.loads((Path(__file__).resolve().parent.parent / "MEASURED_PEAKS.json").read_text()) \
         if (Path(__file__).resolve().parent.parent / "MEASURED_PEAKS.json").exists() else {}
     cases = build_cases()
+    if ns.only:
+        keys = [k.strip().lower() for k in ns.only.split(",") if k.strip()]
+        cases = [c for c in cases if any(k in c[0].lower() for k in keys)]
     for _, _, _, fn in cases:          # warm-up (descriptor caches, first-touch)
         fn()
     torch.cuda.synchronize()

@@ -44,6 +44,11 @@ SHARD_ROW_MULTIPLE = 16          # gather pieces are 16 rows
 MIN_SHARDED_NUMEL = 1 << 16      # smaller tensors stay replicated
 
 
+def padded_rows_per_rank(rows: int, world: int) -> int:
+    per = (rows + world - 1) // world
+    return (per + SHARD_ROW_MULTIPLE - 1) // SHARD_ROW_MULTIPLE * SHARD_ROW_MULTIPLE
+
+
 class _Slot:
     """One pooled heap buffer (a full weight or a full gradient of one size class)."""
 
@@ -64,11 +69,16 @@ class _ShardedWeight:
         n, k = param.shape
         w, r = comm.world_size, comm.rank
         self.name, self.param = name, param
-        self.rows, self.cols, self.rows_per_rank = n, k, n // w
+        # every rank holds the same number of rows, a multiple of the 16-row gather piece; when N does not divide
+        # (GPT-2 XL at 8 ranks: 4800 -> 608 rows/rank, 1600 -> 208) the last rank's shard ends in zero padding rows
+        self.rows, self.cols, self.rows_per_rank = n, k, padded_rows_per_rank(n, w)
+        self.padded_rows = self.rows_per_rank * w
         numel_shard = self.rows_per_rank * k
         self.shard = comm.alloc(numel_shard, torch.bfloat16).view(self.rows_per_rank, k)
         with torch.no_grad():
-            self.shard.copy_(param.data[r * self.rows_per_rank:(r + 1) * self.rows_per_rank])
+            mine = param.data[r * self.rows_per_rank:(r + 1) * self.rows_per_rank]
+            self.shard.zero_()
+            self.shard[: mine.shape[0]].copy_(mine)
         self.master = self.shard.float().clone()
         self.m = torch.zeros_like(self.master) if spec_name == "adamw" else None
         self.v = torch.zeros_like(self.master) if spec_name == "adamw" else None
@@ -125,14 +135,15 @@ class NativeShardedModule(nn.Module):
         named = list(module.named_parameters())
         big = [(n, p) for n, p in named if self._shardable(p, w)]
         small = [(n, p) for n, p in named if not self._shardable(p, w)]
-        classes: Dict[int, int] = {}
+        classes: Dict[int, int] = {}        # pool size class = padded element count of the full matrix
         for _, p in big:
-            classes[p.numel()] = classes.get(p.numel(), 0) + 1
+            key = padded_rows_per_rank(p.shape[0], w) * w * p.shape[1]
+            classes[key] = classes.get(key, 0) + 1
         depth = {numel: (min(max(pool_depth, 1), count) if reshard_after_forward else count)
                  for numel, count in classes.items()}
         # one segment for everything the fused kernels address by offset: shards, full-weight and gradient pools,
         # the flat buffer of the small replicated gradients
-        need = sum(p.numel() * 2 // w + 512 for _, p in big)
+        need = sum(padded_rows_per_rank(p.shape[0], w) * p.shape[1] * 2 + 512 for _, p in big)
         need += sum(2 * d * (numel * 2 + 512) for numel, d in depth.items())
         need += sum(p.numel() * 2 + 512 for _, p in small) + (1 << 20)
         # the init broadcast's staging slab comes out of the same segment (reserved first, so nothing else is mapped)
@@ -157,6 +168,7 @@ class NativeShardedModule(nn.Module):
                     seg, off = comm.locate(buf)
                     if seg is not segment:
                         raise RuntimeError("sharded pools must share the shards' symmetric segment")
+                    buf.zero_()       # padding rows past N stay zero for good: no kernel writes them with data
                     pool.setdefault(numel, []).append(_Slot(buf, off))
         # the full-size original storage goes away: the parameter keeps its shape on a one-element placeholder
         for sw in self.weights.values():
@@ -208,7 +220,7 @@ class NativeShardedModule(nn.Module):
     @staticmethod
     def _shardable(p: torch.Tensor, world: int) -> bool:
         return (p.dim() == 2 and p.dtype == torch.bfloat16 and p.numel() >= MIN_SHARDED_NUMEL
-                and p.shape[0] % (SHARD_ROW_MULTIPLE * world) == 0 and p.shape[1] % 8 == 0)
+                and p.shape[0] >= SHARD_ROW_MULTIPLE * world and p.shape[1] % 8 == 0)
 
     def forward(self, *args: Any, **kwargs: Any) -> Any:
         """Autograd / inference path of the wrapped model: materialises every full weight in ordinary memory for
@@ -235,7 +247,7 @@ class NativeShardedModule(nn.Module):
         """A slot of ``sw``'s size class whose content is no longer needed: unowned first, else the one whose
         (planned) use lies furthest in the past.  Slots stamped at or after ``index`` are in use / prefetched for
         later and are not taken (returns None then, unless this is the access that needs it now)."""
-        slots = pool[sw.rows * sw.cols]
+        slots = pool[sw.padded_rows * sw.cols]
         free = [s for s in slots if s.owner is None]
         if free:
             slot = free[0]
@@ -480,7 +492,8 @@ class NativeShardedModule(nn.Module):
                     t.data.copy_(v)
                     continue
                 rows = v[r * sw.rows_per_rank:(r + 1) * sw.rows_per_rank]
-                sw.shard.copy_(rows)
+                sw.shard.zero_()
+                sw.shard[: rows.shape[0]].copy_(rows)
                 sw.master.copy_(sw.shard.float())
                 if sw.full_slot is not None and sw.full_slot.owner is sw:
                     sw.full_slot.owner = None
@@ -522,7 +535,7 @@ class NativeShardedOptimizer:
                     continue
                 parts = m.comm.gather_to_root(t)
                 if parts is not None:
-                    full.setdefault(sw.name, {})[key] = torch.cat(parts, dim=0)
+                    full.setdefault(sw.name, {})[key] = torch.cat(parts, dim=0)[: sw.rows]     # drop padding rows
         small = m.small_optimizer.state_dict() if (m.small_optimizer is not None and m.comm.rank == 0) else None
         return {"step": m.step_count, "format": "full", "world_size": m.comm.world_size, "state": full, "small": small}
 
@@ -538,10 +551,10 @@ class NativeShardedOptimizer:
         for name, st in sd["state"].items():
             sw = by_name[name]
             rows = slice(r * sw.rows_per_rank, (r + 1) * sw.rows_per_rank)
-            sw.master.copy_(st["master"][rows])
-            if sw.m is not None and "exp_avg" in st:
-                sw.m.copy_(st["exp_avg"][rows])
-            if sw.v is not None and "exp_avg_sq" in st:
-                sw.v.copy_(st["exp_avg_sq"][rows])
+            for dst, key in ((sw.master, "master"), (sw.m, "exp_avg"), (sw.v, "exp_avg_sq")):
+                if dst is not None and key in st:
+                    piece = st[key][rows]
+                    dst.zero_()
+                    dst[: piece.shape[0]].copy_(piece)
         if sd.get("small") is not None and m.small_optimizer is not None:
             m.small_optimizer.load_state_dict(sd["small"])
