@@ -43,17 +43,21 @@ def _workspace(model, B: int, T: int, device: torch.device) -> Dict[str, Any]:
     def act(cols):
         return torch.empty(R, cols, **bf)
 
+    # recompute_gelu: h = gelu(z) is not kept per block (it is 4 of the 16 C-wide activations a block saves); forward
+    # writes it into one shared buffer and backward rebuilds it from z with one elementwise kernel per block
+    recompute = bool(getattr(model, "recompute_gelu", False))
+    h_shared = act(4 * C) if recompute else None
     blocks = []
     for _ in range(L):
         blocks.append({
             "a": act(C), "qkv": torch.empty(B, T, 3 * C, **bf), "att": act(C), "xm": act(C), "m": act(C),
-            "z": act(4 * C), "h": act(4 * C), "x_out": act(C),
+            "z": act(4 * C), "h": h_shared if recompute else act(4 * C), "x_out": act(C),
             "lse": torch.empty(B, H, T, **f32),
             "mean1": torch.empty(R, **f32), "rstd1": torch.empty(R, **f32),
             "mean2": torch.empty(R, **f32), "rstd2": torch.empty(R, **f32),
         })
     ws = {
-        "blocks": blocks,
+        "blocks": blocks, "recompute_gelu": recompute,
         "x0": act(C), "xf": act(C), "meanf": torch.empty(R, **f32), "rstdf": torch.empty(R, **f32),
         "logits": torch.empty(R, V, **bf),
         "row_loss": torch.empty(R, **f32), "loss": torch.empty((), **f32),
@@ -145,6 +149,8 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
     other = dxb
     for blk, a in zip(reversed(list(model.h)), reversed(ws["blocks"])):
         # x_out = xm + h Wpr^T + b   -> dh (with GELU') ; dWpr, dbpr
+        if ws["recompute_gelu"]:
+            native.gelu_fwd(a["z"], a["h"])
         linear_bwd(dx, a["h"], blk.mlp_proj, ws["d4C"], gelu_pre=a["z"])
         # z = m Wfc^T + b            -> dm ; dWfc, dbfc
         linear_bwd(ws["d4C"], a["m"], blk.mlp_fc, ws["dC"])

@@ -29,6 +29,7 @@ points at dead parameters; here the strategy owns shards and optimizer state.
 from __future__ import annotations
 
 import logging
+import os
 from collections import OrderedDict
 from typing import Any, Dict, List, Optional
 
@@ -127,6 +128,9 @@ class NativeShardedModule(nn.Module):
             raise TypeError(f"{type(module).__name__} has no native sharded path")
         self.inner = module
         self.comm = comm
+        if hasattr(module, "recompute_gelu") and os.environ.get("DTB_RECOMPUTE_GELU", "1") != "0":
+            module.recompute_gelu = True      # the sharded strategy is chosen for memory: trade ~2 % time for 25 % of
+            module._ws = {}                   # the saved activations (DTB_RECOMPUTE_GELU=0 keeps gelu(z) per block)
         self.spec = spec or OptimizerSpec("adamw", lr=1e-4)
         self.step_count = 0
         self.reshard_after_forward = reshard_after_forward
