@@ -19,6 +19,14 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
+// 16-byte store to a shared-memory address (32-bit shared window).  A pointer obtained by integer arithmetic on the
+// dynamic shared-memory base is a GENERIC pointer to the compiler: stores through it become ST.E (generic path,
+// stall_lg in ncu) instead of STS.
+__device__ __forceinline__ void st_shared_v4(uint32_t saddr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
   asm volatile(

@@ -22,6 +22,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
+#include <cstdlib>
 
 #include "../../include/dtb200.h"
 #include "../common/host.h"
@@ -576,6 +577,296 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   }
 }
 
+// -------------------------------------------------------------------------- backward, warp-specialised
+// Same math and the same TMEM plan as bwd_kernel, but the jobs of an iteration run in different warps and overlap
+// (ncu on bwd_kernel: 6 % warps active, 16 % issue slots used, tensor pipe 16 %: one 4-warp CTA per SM spent its time
+// waiting on its own MMA -> TMEM -> softmax -> MMA chain):
+//   warps 0-15  "softmax": warp w owns TMEM lane quadrant w & 3 (32 query rows) and 32 of the 128 key columns (w >> 2):
+//               P = exp2(S*c - lse), dS = P (dP - delta) scale, both written to shared memory as bf16
+//   warps 16-19 "dQ": drain the dQ accumulator of the previous step: TMEM -> fp32 tile in shared memory -> ONE bulk
+//               reduce-add (cp.reduce.async.bulk, 32 KB) into the global accumulator.  Per-thread red.global.v4 cost
+//               22 us of a 134 us backward (timing experiment with the atomics disabled)
+//   warp 20     issues every TMA load (3-stage Q / dO ring) and every tcgen05.mma
+// Hand-offs are mbarriers (no __syncthreads in the loop):
+//   sdp_done (MMA commit)       -> softmax: S, dP of this tile are in TMEM
+//   sdp_read (512 arrivals)     -> MMA warp: every softmax thread holds its S / dP values in registers; the NEXT tile's
+//                                  S / dP MMAs go out now, under this tile's exponentials
+//   pds_ready (512 arrivals)    -> MMA warp: P, dS of this tile are in shared memory: dV, dK, dQ MMAs
+//   grads_done (MMA commit)     -> dQ warps: dQ is complete; softmax: P / dS buffers may be overwritten; MMA warp: the
+//                                  Q / dO stage may be refilled (tile + 3)
+//   dq_free (128 arrivals)      -> MMA warp: the dQ columns have been read
+// With everything but the S / dP MMAs and the hand-offs disabled the first warp-specialised version still took
+// 2.8 us per iteration: the 2-stage Q / dO ring exposed the TMA latency and S / dP(i+1) waited for the stores of tile i.
+constexpr int BWD_SOFTMAX_WARPS = 16;        // 4 per TMEM lane quadrant: 32 key columns each
+constexpr int BWD_WS_THREADS = (BWD_SOFTMAX_WARPS + 4 + 1) * 32;
+constexpr int BWD_WS_STAGES = 3;
+// K, V, 3 x (Q, dO), P, dS, fp32 dQ staging tile
+constexpr int BWD_WS_SMEM = TILE_BYTES * (1 + 1 + 2 * BWD_WS_STAGES + 2 + 2 + 2) + 1024 + 256;
+
+__device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, uint32_t ssrc, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gdst), "r"(ssrc),
+               "r"(bytes)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(BWD_WS_THREADS, 1)
+bwd_ws_kernel(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_do,
+              const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_acc,
+              __nv_bfloat16* __restrict__ dqkv, int T, int H, float scale, int dbg) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + TILE_BYTES;
+  uint8_t* sQ = sV + TILE_BYTES;                          // BWD_WS_STAGES stages
+  uint8_t* sdO = sQ + BWD_WS_STAGES * TILE_BYTES;         // BWD_WS_STAGES stages
+  uint8_t* sP = sdO + BWD_WS_STAGES * TILE_BYTES;         // [128 q x 128 kv] bf16
+  uint8_t* sdS = sP + 2 * TILE_BYTES;                     // [128 q x 128 kv] bf16
+  uint8_t* sdQ = sdS + 2 * TILE_BYTES;                    // [128 q x 64] fp32 staging for the bulk reduce
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdQ + 2 * TILE_BYTES);
+  uint64_t* kv_full = bars;
+  uint64_t* qdo_full = bars + 1;             // [BWD_WS_STAGES]
+  uint64_t* sdp_done = bars + 4;
+  uint64_t* sdp_read = bars + 5;
+  uint64_t* pds_ready = bars + 6;
+  uint64_t* grads_done = bars + 7;
+  uint64_t* dq_free = bars + 8;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_bh = gridDim.x / (T / TK);
+  const int jt = static_cast<int>(blockIdx.x) / n_bh;      // longest key tiles first (see fwd_kernel)
+  const int bh = static_cast<int>(blockIdx.x) % n_bh;
+  const int h = bh % H, b = bh / H;
+  const int C = H * HD;
+  const int nT = T / TQ;
+  const int n_q = nT - jt;
+  const int row_base = b * T;
+  constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 320, T_DQ = 384;
+
+  if (tid == 0) {
+    prefetch_tensormap(&map_qkv);
+    prefetch_tensormap(&map_do);
+    mbar_init(kv_full, 1);
+#pragma unroll
+    for (int q = 0; q < BWD_WS_STAGES; ++q) mbar_init(&qdo_full[q], 1);
+    mbar_init(sdp_done, 1);
+    mbar_init(sdp_read, BWD_SOFTMAX_WARPS * 32);
+    mbar_init(pds_ready, BWD_SOFTMAX_WARPS * 32);
+    mbar_init(grads_done, 1);
+    mbar_init(dq_free, 128);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<1>(tmem_ptr, 512);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const float c = scale * LOG2E;
+  const long long stat_base = (static_cast<long long>(b) * H + h) * T;
+
+  if (warp == BWD_SOFTMAX_WARPS + 4) {
+    // ====================================== TMA + MMA issue ======================================
+    const uint32_t k_lo = desc_lo(smem_u32(sK), 16), v_lo = desc_lo(smem_u32(sV), 16);
+    const uint32_t kmn_lo = desc_lo(smem_u32(sK), 8192);
+    const uint32_t p_mn_lo = desc_lo(smem_u32(sP), TILE_BYTES), ds_mn_lo = desc_lo(smem_u32(sdS), TILE_BYTES);
+    const uint32_t ds_k_lo = desc_lo(smem_u32(sdS), 16);
+    auto load_qdo = [&](int tile, int stage) {       // one elected lane
+      mbar_arrive_expect_tx(&qdo_full[stage], 2 * TILE_BYTES);
+      tma_load_4d(sQ + stage * TILE_BYTES, &map_qkv, &qdo_full[stage], h * HD, row_base + (jt + tile) * TQ, 0, 0);
+      tma_load_4d(sdO + stage * TILE_BYTES, &map_do, &qdo_full[stage], h * HD, row_base + (jt + tile) * TQ, 0, 0);
+    };
+    auto issue_sdp = [&](int stage) {                // one elected lane: S = Q K^T, dP = dO V^T
+      const uint32_t q_lo = desc_lo(smem_u32(sQ + stage * TILE_BYTES), 16);
+      const uint32_t do_lo = desc_lo(smem_u32(sdO + stage * TILE_BYTES), 16);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_S, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base + T_DP, desc_k(do_lo, k), desc_k(v_lo, k), IDESC_S, k > 0);
+      umma_commit(sdp_done);
+    };
+    if (elect_one()) {
+      mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+      tma_load_4d(sK, &map_qkv, kv_full, C + h * HD, row_base + jt * TK, 0, 0);
+      tma_load_4d(sV, &map_qkv, kv_full, 2 * C + h * HD, row_base + jt * TK, 0, 0);
+      for (int t = 0; t < BWD_WS_STAGES && t < n_q; ++t) load_qdo(t, t);
+    }
+    __syncwarp();
+    mbar_wait(kv_full, 0);
+    mbar_wait(&qdo_full[0], 0);
+    tcgen05_fence_after();
+    if (elect_one()) issue_sdp(0);
+    __syncwarp();
+    for (int ii = 0; ii < n_q; ++ii) {
+      const int st = ii % BWD_WS_STAGES;
+      const bool more = (ii + 1 < n_q);
+      if (more) {
+        // every softmax thread has S / dP(ii) in registers: the next tile's scores go out under this tile's softmax
+        const int sn = (ii + 1) % BWD_WS_STAGES;
+        mbar_wait(sdp_read, ii & 1);
+        mbar_wait(&qdo_full[sn], ((ii + 1) / BWD_WS_STAGES) & 1);
+        tcgen05_fence_after();
+        if (elect_one()) issue_sdp(sn);
+        __syncwarp();
+      }
+      mbar_wait(pds_ready, ii & 1);            // P / dS(ii) are in shared memory
+      tcgen05_fence_after();
+      const uint32_t qmn_lo = desc_lo(smem_u32(sQ + st * TILE_BYTES), 8192);
+      const uint32_t domn_lo = desc_lo(smem_u32(sdO + st * TILE_BYTES), 8192);
+      if (elect_one() && !(dbg & 2)) {
+        // dV[kv,d] += sum_q P[q,kv] dO[q,d]      A = P^T (MN-major, kv blocks 16 KB apart), B = dO (MN-major)
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16<1>(tmem_base + T_DV, desc_mn(p_mn_lo, k), desc_mn(domn_lo, k), IDESC_TT, (ii | k) != 0);
+        // dK[kv,d] += sum_q dS[q,kv] Q[q,d]
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16<1>(tmem_base + T_DK, desc_mn(ds_mn_lo, k), desc_mn(qmn_lo, k), IDESC_TT, (ii | k) != 0);
+      }
+      __syncwarp();
+      if (ii > 0) {                            // the dQ warps have drained the previous tile's dQ columns
+        mbar_wait(dq_free, (ii - 1) & 1);
+        tcgen05_fence_after();
+      }
+      if (elect_one()) {
+        // dQ[q,d] = sum_kv dS[q,kv] K[kv,d]       A = dS (K-major, two K blocks), B = K (MN-major)
+        if (!(dbg & 4)) {
+#pragma unroll
+          for (int k = 0; k < TK / 16; ++k)
+            umma_f16<1>(tmem_base + T_DQ, desc_k2(ds_k_lo, k), desc_mn(kmn_lo, k), IDESC_PV, k > 0);
+        }
+        umma_commit(grads_done);
+      }
+      __syncwarp();
+      if (ii + BWD_WS_STAGES < n_q) {
+        // the MMAs that read Q / dO of tile ii are done once grads_done flips: refill this stage
+        mbar_wait(grads_done, ii & 1);
+        if (elect_one()) load_qdo(ii + BWD_WS_STAGES, st);
+        __syncwarp();
+      }
+    }
+  }
+  else if (warp < BWD_SOFTMAX_WARPS) {
+    // ========================================= softmax / dS =========================================
+    const int quad = warp & 3, part = warp >> 2;            // part: which 32 of the tile's 128 key columns
+    const int row = quad * 32 + lane;                       // query row inside the tile = TMEM lane
+    const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const uint32_t sP_u32 = smem_u32(sP), sdS_u32 = smem_u32(sdS);
+    const int col0 = part * 32;
+    float next_lse = lse[stat_base + jt * TQ + row], next_delta = delta[stat_base + jt * TQ + row];
+    for (int ii = 0; ii < n_q; ++ii) {
+      const int it = jt + ii;
+      const float row_lse = next_lse * LOG2E;
+      const float row_delta = next_delta;
+      if (ii + 1 < n_q) {
+        next_lse = lse[stat_base + (it + 1) * TQ + row];
+        next_delta = delta[stat_base + (it + 1) * TQ + row];
+      }
+      mbar_wait(sdp_done, ii & 1);
+      tcgen05_fence_after();
+      uint32_t vs[32], vd[32];
+      tmem_ld_32x32b_x32(tmem_row + T_S + col0, vs);
+      tmem_ld_32x32b_x32(tmem_row + T_DP + col0, vd);
+      tmem_ld_wait();
+      tcgen05_fence_before();
+      mbar_arrive(sdp_read);                                 // S / dP columns may be overwritten by the next tile
+      const bool diag = (it == jt);
+      uint32_t pp[16], dd[16];                               // bf16 pairs
+      if (dbg & 1) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) { pp[e] = vs[e]; dd[e] = vd[e]; }
+      } else if (diag) {     // causal mask on the diagonal tile only (uniform branch)
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+          const float p0 = (col0 + e <= row) ? fast_exp2(fmaf(__uint_as_float(vs[e]), c, -row_lse)) : 0.f;
+          const float p1 = (col0 + e + 1 <= row) ? fast_exp2(fmaf(__uint_as_float(vs[e + 1]), c, -row_lse)) : 0.f;
+          pp[e >> 1] = pack2(p0, p1);
+          dd[e >> 1] = pack2(p0 * (__uint_as_float(vd[e]) - row_delta) * scale,
+                             p1 * (__uint_as_float(vd[e + 1]) - row_delta) * scale);
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+          const float p0 = fast_exp2(fmaf(__uint_as_float(vs[e]), c, -row_lse));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(vs[e + 1]), c, -row_lse));
+          pp[e >> 1] = pack2(p0, p1);
+          dd[e >> 1] = pack2(p0 * (__uint_as_float(vd[e]) - row_delta) * scale,
+                             p1 * (__uint_as_float(vd[e + 1]) - row_delta) * scale);
+        }
+      }
+      if (ii > 0) mbar_wait(grads_done, (ii - 1) & 1);       // the MMAs that read P / dS of tile ii-1 are done
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t off = swz_chunk(row, part * 4 + q);
+        st_shared_v4(sP_u32 + off, make_uint4(pp[4 * q], pp[4 * q + 1], pp[4 * q + 2], pp[4 * q + 3]));
+        st_shared_v4(sdS_u32 + off, make_uint4(dd[4 * q], dd[4 * q + 1], dd[4 * q + 2], dd[4 * q + 3]));
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(pds_ready);
+    }
+    // dV (parts 0, 1) / dK (parts 2, 3) of this key tile, 32 columns per warp: TMEM lanes are key rows
+    mbar_wait(grads_done, (n_q - 1) & 1);
+    tcgen05_fence_after();
+    const long long grow = static_cast<long long>(row_base + jt * TK + row);
+    __nv_bfloat16* dst = dqkv + grow * (3 * C) + (part < 2 ? 2 * C : C) + h * HD + (part & 1) * 32;
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(tmem_row + (part < 2 ? T_DV : T_DK) + (part & 1) * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 pk;
+      pk.x = pack2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+      pk.y = pack2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+      pk.z = pack2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+      pk.w = pack2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+      *reinterpret_cast<uint4*>(dst + q * 8) = pk;
+    }
+  } else {
+    // ============================================ dQ drain ============================================
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const uint32_t sdQ_u32 = smem_u32(sdQ);
+    const bool issuer = (warp == BWD_SOFTMAX_WARPS) && (lane == 0);
+    for (int ii = 0; ii < n_q; ++ii) {
+      const int it = jt + ii;
+      mbar_wait(grads_done, ii & 1);
+      tcgen05_fence_after();
+      uint32_t v0[32], v1[32];
+      tmem_ld_32x32b_x32(tmem_row + T_DQ, v0);
+      tmem_ld_32x32b_x32(tmem_row + T_DQ + 32, v1);
+      tmem_ld_wait();
+      tcgen05_fence_before();
+      mbar_arrive(dq_free);                    // the next dQ MMA may overwrite the columns
+      if (dbg & 8) continue;
+      // the previous bulk reduce must have finished READING the staging tile before it is overwritten
+      if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // plain row-major [128][64] fp32: the bulk reduce adds the tile to global memory byte for byte, so no swizzle
+      // (the lanes of a warp write rows 256 B apart: bank conflicts, but in warps that are off the critical path)
+      const uint32_t rbase = sdQ_u32 + row * 256;
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        st_shared_v4(rbase + q * 16, make_uint4(v0[4 * q], v0[4 * q + 1], v0[4 * q + 2], v0[4 * q + 3]));
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        st_shared_v4(rbase + (q + 8) * 16, make_uint4(v1[4 * q], v1[4 * q + 1], v1[4 * q + 2], v1[4 * q + 3]));
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (issuer) {
+        bulk_reduce_add_f32(dq_acc + (stat_base + it * TQ) * HD, sdQ_u32, TQ * HD * 4);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
 static int make_map(CUtensorMap* map, const void* base, long long rows, long long cols) {
   const uint64_t dims[4] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(rows), 1, 1};
   const uint64_t strides[3] = {static_cast<uint64_t>(cols) * 2, static_cast<uint64_t>(cols) * 2 * rows,
@@ -640,8 +931,25 @@ extern "C" int dtb_attention_bwd(const void* qkv, const void* out, const void* d
       heads);
   DTB_LAUNCH_OK();
   dim3 grid(static_cast<unsigned>(seq / TK) * heads * batch);
-  bwd_kernel<<<grid, 128, BWD_SMEM, s>>>(map_qkv, map_do, lse, delta, dq_acc, static_cast<__nv_bfloat16*>(dqkv), seq,
-                                         heads, 1.0f / sqrtf(static_cast<float>(HD)));
+  // DTB_ATTN_BWD_WS=1 selects the warp-specialised kernel (bwd_ws_kernel).  Its first two versions (TMEM -> red.global
+  // dQ, 2-stage Q / dO ring) were validated on a B200 against the fp32 oracle (134-136 us vs 138 us for bwd_kernel); the
+  // current one (3-stage ring, early S / dP issue, bulk-reduce dQ) was written after GPU access closed for the round and
+  // has NOT run on hardware yet, so the validated 4-warp kernel stays the default.
+  static const bool ws = [] { const char* e = getenv("DTB_ATTN_BWD_WS"); return e && e[0] == '1'; }();
+  static const int dbg = [] { const char* e = getenv("DTB_ATTN_DBG"); return e ? atoi(e) : 0; }();   // timing experiments
+  if (ws) {
+    static bool ws_configured = false;
+    if (!ws_configured) {
+      DTB_CUDA_OK(cudaFuncSetAttribute(bwd_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_WS_SMEM));
+      ws_configured = true;
+    }
+    bwd_ws_kernel<<<grid, BWD_WS_THREADS, BWD_WS_SMEM, s>>>(map_qkv, map_do, lse, delta, dq_acc,
+                                                         static_cast<__nv_bfloat16*>(dqkv), seq, heads,
+                                                         1.0f / sqrtf(static_cast<float>(HD)), dbg);
+  } else {
+    bwd_kernel<<<grid, 128, BWD_SMEM, s>>>(map_qkv, map_do, lse, delta, dq_acc, static_cast<__nv_bfloat16*>(dqkv), seq,
+                                           heads, 1.0f / sqrtf(static_cast<float>(HD)));
+  }
   DTB_LAUNCH_OK();
   const long long vecs = bt * heads * (HD / 8);
   bwd_finish_kernel<<<static_cast<int>((vecs + 255) / 256), 256, 0, s>>>(dq_acc, static_cast<__nv_bfloat16*>(dqkv), batch,
