@@ -43,6 +43,10 @@ def build_cases():
     cases.append(("gemm wgrad 8192x8192x4096 fused SGD (W -= lr dW)", fl, 0,
                   lambda: native.gemm(dy, x, w, m=D, n=D, k=M, a_mn=True, b_mn=True, aux=w, alpha=-1e-6, beta=1.0)))
     db = torch.empty(D, device=dev, dtype=BF)
+    bsum = torch.zeros(D, device=dev, dtype=F32)
+    cases.append(("gemm dgrad 4096x8192x8192 *gelu'(aux) + column sums (bias grad) in the epilogue", fl, 0,
+                  lambda: native.gemm(dy, w, dx, m=M, n=D, k=D, b_mn=True, aux=pre, act=2, colsum=bsum)))
+    cases.append(("take fp32 colsum -> bf16 bias grad 8192", 0, D * 10, lambda: native.take_f32_to_bf16(bsum, db)))
     cases.append(("colsum 4096x8192 (bias grad)", 0, M * D * 2, lambda: native.colsum_split(dy, db)))
     logits, tgt, rl = rn(M, D), torch.randint(0, D, (M,), device=dev), torch.empty(M, device=dev, dtype=F32)
     cases.append(("cross-entropy fwd+bwd 4096x8192", 0, 2 * M * D * 2,

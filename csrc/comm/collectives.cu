@@ -565,14 +565,31 @@ reduce_scatter_kernel(const Ctx x, size_t src_off, long long nvec, void* out, in
         w[j] = t.x; w[j + 1] = t.y; w[j + 2] = t.z; w[j + 3] = t.w;
       }
       if (o.opt == 1) {
+        // torch.optim.AdamW's update with the element-independent factors folded once per thread and approximate
+        // sqrt / rcp (1-2 ulp): the IEEE form cost ~180 instructions per element and the comm CTAs share their SMs
+        float m[N], vv[N];
+#pragma unroll
+        for (int j = 0; j < N; j += 4) {
+          const float4 a = *reinterpret_cast<const float4*>(o.m + e + j);
+          const float4 b = *reinterpret_cast<const float4*>(o.v + e + j);
+          m[j] = a.x; m[j + 1] = a.y; m[j + 2] = a.z; m[j + 3] = a.w;
+          vv[j] = b.x; vv[j + 1] = b.y; vv[j + 2] = b.z; vv[j + 3] = b.w;
+        }
+        const float omb1 = 1.f - o.beta1, omb2 = 1.f - o.beta2, decay = 1.f - o.lr * o.wd;
+        const float step = o.lr / o.bc1, rs_bc2 = rsqrtf(o.bc2);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          float m = o.m[e + j], vv = o.v[e + j];
-          m = o.beta1 * m + (1.f - o.beta1) * g[j];
-          vv = o.beta2 * vv + (1.f - o.beta2) * g[j] * g[j];
-          o.m[e + j] = m;
-          o.v[e + j] = vv;
-          w[j] = w[j] * (1.f - o.lr * o.wd) - o.lr * (m / o.bc1) / (sqrtf(vv / o.bc2) + o.eps);
+          m[j] = fmaf(o.beta1, m[j], omb1 * g[j]);
+          vv[j] = fmaf(o.beta2, vv[j], omb2 * g[j] * g[j]);
+          float sq, rc;
+          asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(vv[j]));
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(fmaf(sq, rs_bc2, o.eps)));
+          w[j] = fmaf(w[j], decay, -step * m[j] * rc);
+        }
+#pragma unroll
+        for (int j = 0; j < N; j += 4) {
+          *reinterpret_cast<float4*>(o.m + e + j) = make_float4(m[j], m[j + 1], m[j + 2], m[j + 3]);
+          *reinterpret_cast<float4*>(o.v + e + j) = make_float4(vv[j], vv[j + 1], vv[j + 2], vv[j + 3]);
         }
       } else {
 #pragma unroll
@@ -833,6 +850,8 @@ extern "C" int dtb_comm_rs_optim(const dtb_comm* c, size_t grad_offset, size_t s
   DTB_REQUIRE(grad_offset % 16 == 0 && shard_offset % 16 == 0 && n % 8 == 0, "dtb_comm_rs_optim: shard must be 16-byte granular");
   DTB_REQUIRE(master != nullptr, "dtb_comm_rs_optim: fp32 master shard is required");
   DTB_REQUIRE(opt == 0 || (m != nullptr && v != nullptr), "dtb_comm_rs_optim: AdamW needs both moments");
+  DTB_REQUIRE(((reinterpret_cast<uintptr_t>(master) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
+              "dtb_comm_rs_optim: master and moment shards must be 16-byte aligned");
   if (n == 0) return 0;
   Ctx x = {*c, channel_of(max_ctas)};
   const long long nvec = n * 2 / 16;

@@ -272,6 +272,25 @@ extern "C" int dtb_cast_f32_to_bf16(const float* in, void* out, long long n, voi
   return 0;
 }
 
+// bf16(in) -> out, then in = 0 (hand-over of the fp32 bias-gradient accumulator the GEMM epilogue adds into)
+__global__ void __launch_bounds__(256) take_f32_bf16_kernel(float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                            long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) {
+    out[i] = __float2bfloat16(in[i]);
+    in[i] = 0.f;
+  }
+}
+
+extern "C" int dtb_take_f32_to_bf16(float* in, void* out, long long n, void* stream) {
+  if (n <= 0) return 0;
+  DTB_REQUIRE(in != nullptr && out != nullptr, "dtb_take_f32_to_bf16: null argument");
+  take_f32_bf16_kernel<<<static_cast<int>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      in, static_cast<__nv_bfloat16*>(out), n);
+  DTB_LAUNCH_OK();
+  return 0;
+}
+
 extern "C" int dtb_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream) {
   if (n <= 0) return 0;
   cast_bf16_f32_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(

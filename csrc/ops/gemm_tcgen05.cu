@@ -61,6 +61,9 @@ struct Params {
   int g_world, g_rank, g_rows_per_rank;
   int g_rotate;            // n-blocks to rotate the visiting order by (rank * blocks_per_rank); -1 = off
   int direct_epilogue;     // 1 = per-thread row stores (no shared-memory staging); DTB_GEMM_DIRECT_EPILOGUE=1
+  // ---- column sums of D (bias gradient of the layer D is the output gradient of): fp32 [N], added with vector
+  // reductions from the staged epilogue's store loop, where a lane already holds 8 rows x 8 columns of the tile
+  float* colsum;
   // ---- split-K: work unit = (tile, split); split s accumulates k-blocks [s*kb_per_split, ...) and writes its
   // raw fp32 accumulators to ws[s][M][N]; splitk_reduce_kernel adds the slices in order and runs the epilogue.
   int split_k, kb_per_split;
@@ -429,6 +432,15 @@ __device__ __forceinline__ void epilogue_group_compute(const Params& p, const Ep
   __syncwarp();
 }
 
+__device__ __forceinline__ void add_bf16x8(float (&acc)[8], const uint4& v) {
+  const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    acc[2 * j] += __uint_as_float(u[j] << 16);
+    acc[2 * j + 1] += __uint_as_float(u[j] & 0xffff0000u);
+  }
+}
+
 // shared memory -> global memory for column group c2: 8 steps of 4 rows x 128 bytes per warp
 __device__ __forceinline__ void epilogue_group_store(const Params& p, const EpiTile& t, int c2, const uint8_t* st_out,
                                                      const uint8_t* st_in, int lane) {
@@ -438,22 +450,46 @@ __device__ __forceinline__ void epilogue_group_store(const Params& p, const EpiT
   const uint32_t even = static_cast<uint32_t>(sub * 128 + ((seg ^ sub) << 4)), odd = even ^ 64u;
   uint8_t* dp = t.out + c2 * 128;
   uint8_t* zp = t.out2 + c2 * 128;
+  const bool cs_on = p.colsum != nullptr;
+  float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const int gc = t.n0 + c2 * 64 + seg * 8;
   if (t.interior) {
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const uint32_t so = ((it & 1) ? odd : even) + it * 512;
-      *reinterpret_cast<uint4*>(dp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_out + so);
+      const uint4 o = *reinterpret_cast<const uint4*>(st_out + so);
+      *reinterpret_cast<uint4*>(dp + it * t.step_d) = o;
       if (want_z) *reinterpret_cast<uint4*>(zp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_in + so);
+      if (cs_on) add_bf16x8(cs, o);
     }
   } else {
-    const int gc = t.n0 + c2 * 64 + seg * 8;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const uint32_t so = ((it & 1) ? odd : even) + it * 512;
       if (t.row_base + it * 4 + sub < p.M && gc < p.N) {
-        *reinterpret_cast<uint4*>(dp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_out + so);
+        const uint4 o = *reinterpret_cast<const uint4*>(st_out + so);
+        *reinterpret_cast<uint4*>(dp + it * t.step_d) = o;
         if (want_z) *reinterpret_cast<uint4*>(zp + it * t.step_d) = *reinterpret_cast<const uint4*>(st_in + so);
+        if (cs_on) add_bf16x8(cs, o);
       }
+    }
+  }
+  if (cs_on) {
+    // lanes with the same `seg` hold the other 24 rows of these 8 columns: fold them, then one lane per segment
+    // sends two 16-byte reductions.  32 x 256 of them per 128 x 256 tile: invisible next to a K >= 4096 main loop.
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
+      cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+    }
+    if (sub == 0 && gc < p.N) {
+      float* dst = p.colsum + gc;
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(cs[0]), "f"(cs[1]), "f"(cs[2]),
+                   "f"(cs[3])
+                   : "memory");
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4), "f"(cs[4]), "f"(cs[5]), "f"(cs[6]),
+                   "f"(cs[7])
+                   : "memory");
     }
   }
   __syncwarp();
@@ -1094,7 +1130,7 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   int bn = a->tile_n;
   const int num_kb_total = (a->k + BK - 1) / BK;
   // split-K needs a workspace, a plain (unbatched, non-gather) problem and 16-byte-granular rows
-  const bool can_split = g == nullptr && bi * bo == 1 && a->workspace != nullptr && a->split_k != 1 &&
+  const bool can_split = g == nullptr && bi * bo == 1 && a->workspace != nullptr && a->split_k != 1 && a->colsum == nullptr &&
                          (a->n % 8) == 0 && num_kb_total >= 8;
   if (bn == 0) {
     const long long tiles256 = 1LL * ((a->m + 127) / 128) * ((a->n + 255) / 256) * bi * bo;
@@ -1152,6 +1188,12 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   p.d_fp32 = a->d_fp32; p.aux_fp32 = a->aux_fp32; p.bias_fp32 = a->bias_fp32;
   p.act = a->act;
   p.alpha = a->alpha; p.beta = a->beta;
+  p.colsum = a->colsum;
+  if (a->colsum != nullptr) {
+    DTB_REQUIRE(bi * bo == 1 && !a->d_fp32 && !(a->aux != nullptr && a->aux_fp32) && a->n % 8 == 0 &&
+                    (reinterpret_cast<uintptr_t>(a->colsum) & 15) == 0,
+                "dtb_gemm_bf16: colsum needs an unbatched bf16 D with N %% 8 == 0 and a 16-byte aligned fp32 [N] buffer");
+  }
   // canonical 128B-swizzle layouts (cute/atom/mma_traits_sm100.hpp):
   //   K-major : 8-row groups 1024 B apart (SBO); LBO unused (1)
   //   MN-major: 64-wide MN blocks 8192 B apart (LBO); 8-row K groups 1024 B apart (SBO)
@@ -1165,7 +1207,7 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
   p.ws = static_cast<float*>(a->workspace);
   {
     static const int direct = [] { const char* e = getenv("DTB_GEMM_DIRECT_EPILOGUE"); return (e && e[0] == '1') ? 1 : 0; }();
-    p.direct_epilogue = direct;
+    p.direct_epilogue = a->colsum != nullptr ? 0 : direct;
   }
   if (g != nullptr) {
     DTB_REQUIRE(!a->a_mn_major && !a->b_mn_major && bi * bo == 1,
@@ -1199,7 +1241,7 @@ static int gemm_impl(const dtb_gemm_args* a, const dtb_gather_args* g, void* str
     p.tma_store = 0;
     // long-K GEMMs hide their epilogue anyway, and in the power-capped wide-MLP step the per-lane hand-off measured
     // 0.7 % faster (9.745 vs 9.82 ms on the same box), so the TMA unit takes over only below K = 4096
-    if (tma_store && staged && strides_ok && a->k < 4096) {
+    if (tma_store && staged && strides_ok && a->k < 4096 && a->colsum == nullptr) {
       uint64_t dims[4] = {static_cast<uint64_t>(a->n), static_cast<uint64_t>(a->m), static_cast<uint64_t>(bi),
                           static_cast<uint64_t>(bo)};
       uint32_t box[4] = {64, 32, 1, 1};

@@ -12,6 +12,9 @@
 #include <cuda_runtime.h>
 #include <float.h>
 
+#include <algorithm>
+#include <cstdlib>
+
 #include "../../include/dtb200.h"
 #include "../common/host.h"
 
@@ -123,6 +126,184 @@ ce_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targ
   }
 }
 
+// ---- streaming CE: persistent CTAs, rows double-buffered in shared memory by bulk async copies --------------------
+// The ncu capture of ce_kernel (profiles/kernel_zoo_ncu_metrics.csv) shows it issue-bound, not bandwidth-bound:
+// 31 instructions and 2.25 MUFU.EX2 per logit (online max/sum-exp in the load loop, a second exponential in the
+// gradient loop, non-ftz ex2 sequences), 0.48 of the HBM copy rate.  This kernel does one exponential and ~10
+// instructions per logit:
+//   copy   cp.async.bulk global -> shared of row i+1 (one elected thread, mbarrier complete_tx) under the math of row i
+//   pass 1 packed bf16x2 max over the shared row (padding columns [vocab, ld) are set to -inf here)
+//   pass 2 e = ex2(x*log2e - max*log2e): summed in fp32, written back over the row as bf16
+//   pass 3 dlogits = e * grad_scale/sum (fp32 multiply, one rounding), 16-byte stores straight to the row in HBM; the
+//          target column is recomputed from its fp32 logit so that p_t - 1 keeps full precision when p_t -> 1.
+namespace {
+
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ void bulk_load_row(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(sdst))),
+               "l"(gsrc), "r"(bytes), "r"(static_cast<uint32_t>(__cvta_generic_to_shared(bar)))
+               : "memory");
+}
+__device__ __forceinline__ void bar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(bar))),
+               "r"(count)
+               : "memory");
+}
+__device__ __forceinline__ void bar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(bar))),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(done)
+        : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(bar))), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+
+template <int T>
+__device__ __forceinline__ float block_max(float v, float* red) {   // one __syncthreads; every thread gets the result
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = (threadIdx.x & 31) < T / 32 ? red[threadIdx.x & 31] : -FLT_MAX;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
+  return r;
+}
+template <int T>
+__device__ __forceinline__ float block_sum(float v, float* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = (threadIdx.x & 31) < T / 32 ? red[threadIdx.x & 31] : 0.f;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  return r;
+}
+
+}  // namespace
+
+template <int T>
+__global__ void __launch_bounds__(T, T == 256 ? 4 : 1)
+ce_stream_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
+                 float* __restrict__ row_loss, int rows, int vocab, long long ld, float grad_scale, int write_grad) {
+  extern __shared__ __align__(128) uint8_t ce_smem[];
+  __shared__ __align__(8) uint64_t full[2];
+  __shared__ float red_m[2][32], red_s[2][32];
+  constexpr float LOG2E = 1.4426950408889634f;
+  const uint32_t row_bytes = static_cast<uint32_t>(ld) * 2;
+  const int nvec = static_cast<int>(ld >> 3);
+  const int first_pad_vec = vocab >> 3;             // vectors from here on contain padding columns
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    bar_init(&full[0], 1);
+    bar_init(&full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  int row = blockIdx.x;
+  if (row >= rows) return;
+  if (tid == 0) {
+    bar_expect_tx(&full[0], row_bytes);
+    bulk_load_row(ce_smem, logits + static_cast<long long>(row) * ld, row_bytes, &full[0]);
+  }
+  long long tgt_next = targets[row];
+  for (int it = 0; row < rows; ++it, row += gridDim.x) {
+    const int s = it & 1;
+    uint8_t* srow = ce_smem + static_cast<size_t>(s) * row_bytes;
+    const int next = row + gridDim.x;
+    const int tgt = static_cast<int>(tgt_next);
+    if (next < rows) tgt_next = targets[next];       // in flight under this row's passes
+    if (tid == 0 && next < rows) {
+      // every thread finished reading / writing the other buffer before the __syncthreads that ended the previous
+      // iteration; order those generic-proxy accesses before the async-proxy write
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      bar_expect_tx(&full[s ^ 1], row_bytes);
+      bulk_load_row(ce_smem + static_cast<size_t>(s ^ 1) * row_bytes, logits + static_cast<long long>(next) * ld,
+                    row_bytes, &full[s ^ 1]);
+    }
+    const bool ignore = tgt < 0 || tgt >= vocab;      // ignore_index < 0
+    bar_wait(&full[s], (it >> 1) & 1);
+    const float xt = ignore ? 0.f : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(srow)[tgt]);
+    // ---- pass 1: max ----
+    __nv_bfloat162 mx2 = __float2bfloat162_rn(-FLT_MAX);
+    for (int v = tid; v < nvec; v += T) {
+      uint4 raw = *reinterpret_cast<const uint4*>(srow + v * 16);
+      if (v >= first_pad_vec) {
+        __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(&raw);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v * 8 + j >= vocab) e[j] = __ushort_as_bfloat16(0xff80);   // -inf: no weight in max, sum or gradient
+        *reinterpret_cast<uint4*>(srow + v * 16) = raw;
+      }
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+      mx2 = __hmax2(mx2, __hmax2(__hmax2(h[0], h[1]), __hmax2(h[2], h[3])));
+    }
+    const float m = block_max<T>(fmaxf(__low2float(mx2), __high2float(mx2)), red_m[s]);
+    const float ml2 = m * LOG2E;
+    // ---- pass 2: exponentials, sum ----
+    float sum = 0.f;
+    for (int v = tid; v < nvec; v += T) {
+      uint4 raw = *reinterpret_cast<const uint4*>(srow + v * 16);
+      uint32_t u[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float e0 = ex2_ftz(fmaf(__uint_as_float(u[j] << 16), LOG2E, -ml2));
+        const float e1 = ex2_ftz(fmaf(__uint_as_float(u[j] & 0xffff0000u), LOG2E, -ml2));
+        sum += e0 + e1;
+        const __nv_bfloat162 pk = __floats2bfloat162_rn(e0, e1);
+        u[j] = *reinterpret_cast<const uint32_t*>(&pk);
+      }
+      if (write_grad) *reinterpret_cast<uint4*>(srow + v * 16) = make_uint4(u[0], u[1], u[2], u[3]);
+    }
+    sum = block_sum<T>(sum, red_s[s]);
+    if (tid == 0) row_loss[row] = ignore ? 0.f : (m + __logf(sum)) - xt;
+    // ---- pass 3: gradient, in place over the logits row ----
+    if (write_grad) {
+      const float inv = ignore ? 0.f : grad_scale / sum;
+      uint8_t* grow = reinterpret_cast<uint8_t*>(logits + static_cast<long long>(row) * ld);
+      const int tvec = ignore ? -1 : (tgt >> 3);
+      for (int v = tid; v < nvec; v += T) {
+        const uint4 raw = *reinterpret_cast<const uint4*>(srow + v * 16);
+        const uint32_t u[4] = {raw.x, raw.y, raw.z, raw.w};
+        uint4 out;
+        uint32_t* o = reinterpret_cast<uint32_t*>(&out);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const __nv_bfloat162 pk = __floats2bfloat162_rn(__uint_as_float(u[j] << 16) * inv,
+                                                          __uint_as_float(u[j] & 0xffff0000u) * inv);
+          o[j] = *reinterpret_cast<const uint32_t*>(&pk);
+        }
+        if (v == tvec) {
+          const float g = ex2_ftz(fmaf(xt, LOG2E, -ml2)) * inv - grad_scale;
+          const uint32_t gb = __bfloat16_as_ushort(__float2bfloat16(g));
+          const int word = (tgt & 7) >> 1;
+          const uint32_t keep = (tgt & 1) ? 0x0000ffffu : 0xffff0000u, put = (tgt & 1) ? gb << 16 : gb;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j == word) o[j] = (o[j] & keep) | put;
+        }
+        *reinterpret_cast<uint4*>(grow + v * 16) = out;
+      }
+    }
+    __syncthreads();      // this buffer may be refilled (two iterations from now it is loaded again)
+  }
+}
+
 // Soft-label CE over small class counts: one warp per row, fp32.
 __global__ void __launch_bounds__(128)
 soft_ce_kernel(const float* __restrict__ logits, const float* __restrict__ targets, float* __restrict__ row_loss,
@@ -192,15 +373,47 @@ extern "C" int dtb_cross_entropy_fwd_bwd(void* logits, const long long* targets,
               vocab, ld);
   DTB_REQUIRE(ld % 8 == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0,
               "dtb_cross_entropy: logits must be 16-byte aligned with ld %% 8 == 0");
-  const size_t smem = static_cast<size_t>(ld) * 2;
-  DTB_REQUIRE(smem <= 200 * 1024, "dtb_cross_entropy: vocab %d exceeds the shared-memory row cache", vocab);
+  const size_t row_bytes = static_cast<size_t>(ld) * 2;
+  DTB_REQUIRE(row_bytes <= 200 * 1024, "dtb_cross_entropy: vocab %d exceeds the shared-memory row cache", vocab);
+  auto s = static_cast<cudaStream_t>(stream);
+  auto* lg = static_cast<__nv_bfloat16*>(logits);
+  static const bool legacy = [] {
+    const char* e = getenv("DTB_CE_LEGACY");
+    return e && e[0] == '1';
+  }();
+  // two row buffers must fit (227 KB per CTA): GPT-2's 50304-wide rows take 2 x 100.6 KB, one 1024-thread CTA per SM
+  if (!legacy && 2 * row_bytes <= 225 * 1024 && row_bytes >= 16 * 1024) {
+    const size_t smem = 2 * row_bytes;
+    const bool big = row_bytes >= 48 * 1024;
+    static size_t configured_big = 0, configured_small = 0;
+    if (big && smem > configured_big) {
+      DTB_CUDA_OK(cudaFuncSetAttribute(ce_stream_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+      configured_big = 225 * 1024;
+    }
+    if (!big && smem > 48 * 1024 && smem > configured_small) {
+      DTB_CUDA_OK(cudaFuncSetAttribute(ce_stream_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      configured_small = 96 * 1024;
+    }
+    if (big) {
+      const int grid = rows < sm_count() ? rows : sm_count();
+      ce_stream_kernel<1024><<<grid, 1024, smem, s>>>(lg, targets, row_loss, rows, vocab, ld, grad_scale, write_grad);
+    } else {
+      // small rows: several 256-thread CTAs per SM (shared memory and the 2048-thread limit allow up to 6-8)
+      const int per_sm = static_cast<int>(std::min<size_t>(8, (200 * 1024) / (smem + 1024)));
+      const int cap = sm_count() * (per_sm < 1 ? 1 : per_sm);
+      const int grid = rows < cap ? rows : cap;
+      ce_stream_kernel<256><<<grid, 256, smem, s>>>(lg, targets, row_loss, rows, vocab, ld, grad_scale, write_grad);
+    }
+    DTB_LAUNCH_OK();
+    return 0;
+  }
+  const size_t smem = row_bytes;
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
     DTB_CUDA_OK(cudaFuncSetAttribute(ce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     configured = 200 * 1024;
   }
-  ce_kernel<<<rows, CE_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<__nv_bfloat16*>(logits), targets, row_loss, vocab, ld, grad_scale, write_grad);
+  ce_kernel<<<rows, CE_THREADS, smem, s>>>(lg, targets, row_loss, vocab, ld, grad_scale, write_grad);
   DTB_LAUNCH_OK();
   return 0;
 }

@@ -12,6 +12,7 @@ handed to the reducer the moment a layer's wgrad has been queued.
 """
 from __future__ import annotations
 
+import os
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -19,6 +20,8 @@ import torch.nn.functional as F
 from torch import nn
 
 from ..ops import native
+
+_FUSED_COLSUM = os.environ.get("DTB_FUSED_COLSUM", "1") != "0"
 
 
 class MLP(nn.Module):
@@ -69,9 +72,19 @@ class MLP(nn.Module):
                 "dz": [torch.empty(rows, max(self.dims[1:-1] or [8]), **bf) for _ in range(2)],
                 "row_loss": torch.empty(rows, dtype=torch.float32, device=device),
                 "loss": torch.empty((), dtype=torch.float32, device=device),
+                # fp32 bias-gradient accumulators the dgrad epilogues add into (zero between steps)
+                "bsum": [torch.zeros(self.dims[i + 1], dtype=torch.float32, device=device) for i in range(n - 1)],
             }
             self._ws = {key: ws}      # one live batch shape at a time
         return ws
+
+    def _fuse_bias_grad(self, i: int, k_of_dgrad: int) -> bool:
+        """Layer ``i``'s bias gradient comes out of the epilogue of the dgrad GEMM that produces its output gradient
+        (``dtb_gemm_args.colsum``) when that GEMM's K is long enough to hide the extra epilogue work and the
+        gradient is bf16; DTB_FUSED_COLSUM=0 keeps the separate column-sum kernel."""
+        bias = self.layers[i].bias
+        return (_FUSED_COLSUM and bias is not None and bias.dtype == torch.bfloat16 and k_of_dgrad >= 2048
+                and self.dims[i + 1] % 8 == 0)
 
     #: forward_backward accepts ``bwd_max_ctas`` (see ReplicatedModule: exclusive-mode reduction kernels)
     supports_bwd_max_ctas = True
@@ -132,9 +145,13 @@ class MLP(nn.Module):
             if i > 0:
                 # dgrad fused with GELU': dz_prev = (dz W_i) * gelu'(z_{i-1}).  It runs BEFORE this layer's
                 # wgrad is handed to the reducer: a fused reduce+SGD (or the fused epilogue below) overwrites W_i.
+                # The same epilogue adds dz_prev's column sums (= the bias gradient of layer i-1) to an fp32
+                # accumulator: no separate pass over dz_prev.
                 nxt = ws["dz"][i % 2]
+                fuse_bias = self._fuse_bias_grad(i - 1, out_f)
                 native.gemm(dz, wv(layer.weight), nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
-                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=cap)
+                            ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=cap,
+                            colsum=ws["bsum"][i - 1] if fuse_bias else None)
             if fused_sgd is not None:
                 # single replica: W = (1 - lr*wd) W - lr * (dz^T h_in), applied in the wgrad epilogue (no dW in HBM)
                 lr, wd = fused_sgd
@@ -157,7 +174,15 @@ class MLP(nn.Module):
                 native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
                             lda=dz.shape[1], ldb=in_f, max_ctas=cap)
             if layer.bias is not None:
-                native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
+                if i < n - 1 and self._fuse_bias_grad(i, self.dims[i + 2]):
+                    gb = grad_of(layer.bias)
+                    if gb.dtype == torch.bfloat16:
+                        native.take_f32_to_bf16(ws["bsum"][i], gb)
+                    else:
+                        gb.copy_(ws["bsum"][i])
+                        ws["bsum"][i].zero_()
+                else:
+                    native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
             if grad_sink is not None:
                 grad_sink.mark_ready(layer.weight)
                 if layer.bias is not None:

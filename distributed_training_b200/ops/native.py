@@ -44,6 +44,7 @@ class GemmArgs(C.Structure):
         ("tile_n", C.c_int), ("cta_pair", C.c_int), ("max_ctas", C.c_int),
         ("dbg_lbo_a", C.c_uint), ("dbg_sbo_a", C.c_uint), ("dbg_lbo_b", C.c_uint), ("dbg_sbo_b", C.c_uint),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_longlong), ("split_k", C.c_int),
+        ("colsum", C.c_void_p),
     ]
 
 
@@ -147,8 +148,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, m: int, n: int,
          a_strides: Tuple[int, int] = (0, 0), b_strides: Tuple[int, int] = (0, 0),
          d_strides: Tuple[int, int] = (0, 0), aux_strides: Tuple[int, int] = (0, 0),
          tile_n: int = 0, cta_pair: int = 0, max_ctas: int = 0, dbg: Tuple[int, int, int, int] = (0, 0, 0, 0),
-         split_k: int = 0) -> torch.Tensor:
+         split_k: int = 0, colsum: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``out[m,n] = epilogue(alpha * sum_k A(m,k) B(n,k))`` — see ``dtb_gemm_bf16`` in the header.
+
+    ``colsum`` (fp32 ``[n]``, zeroed by the caller): the epilogue adds the column sums of ``out`` to it.
 
     ``a``/``b`` are bf16; layouts are described by ``*_mn`` and the leading
     dimensions (default: dense rows of the logical storage shape).
@@ -181,6 +184,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, m: int, n: int,
         ws = _gemm_workspace(a.device)
         args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel() * 4
     args.split_k = split_k
+    if colsum is not None:
+        assert colsum.dtype == torch.float32 and colsum.numel() >= n
+        args.colsum = colsum.data_ptr()
     _ok(lib().dtb_gemm_bf16(C.byref(args), _stream()))
     return out
 
@@ -287,6 +293,13 @@ def colsum_split(x2d: torch.Tensor, out: torch.Tensor, ldx: Optional[int] = None
 
 def cast_f32_to_bf16(src, dst):
     _ok(lib().dtb_cast_f32_to_bf16(_p(src), _p(dst), C.c_longlong(src.numel()), _stream()))
+    return dst
+
+
+def take_f32_to_bf16(src, dst):
+    """``dst = bf16(src); src = 0`` (hand-over of a GEMM ``colsum`` accumulator to a bf16 gradient)."""
+    assert src.dtype == torch.float32 and dst.dtype == torch.bfloat16 and dst.numel() >= src.numel()
+    _ok(lib().dtb_take_f32_to_bf16(_p(src), _p(dst), C.c_longlong(src.numel()), _stream()))
     return dst
 
 

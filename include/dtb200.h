@@ -66,6 +66,11 @@ typedef struct dtb_gemm_args {
   void* workspace;
   long long workspace_bytes;
   int split_k;
+  /* optional fp32 [N], 16-byte aligned: the column sums of D (as rounded to bf16) are ADDED to it from the epilogue
+   * with vector reductions -- the bias gradient when D is an output gradient (replaces a dtb_colsum_bf16 pass over
+   * D).  The caller zeroes it (dtb_take_f32_to_bf16 re-zeroes while converting).  Needs bf16 D, no batching; turns
+   * split-K and the direct epilogue off.  Summation order is not fixed (fp32 atomics). */
+  float* colsum;
 } dtb_gemm_args;
 int dtb_gemm_bf16(const dtb_gemm_args* args, void* stream);
 
@@ -109,6 +114,9 @@ int dtb_colsum_bf16_split(const void* x, void* out, int rows, int cols, long lon
 int dtb_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
 int dtb_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 int dtb_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
+/* out[i] = bf16(in[i]); in[i] = 0: hands an fp32 accumulator (dtb_gemm_args.colsum) over to a bf16 gradient and
+ * leaves it ready for the next step. */
+int dtb_take_f32_to_bf16(float* in, void* out, long long n, void* stream);
 /* sum of squares of n elements into *out (fp32, accumulated with atomicAdd; caller zeroes). K15. */
 int dtb_sumsq(const void* x, int is_fp32, long long n, float* out, void* stream);
 

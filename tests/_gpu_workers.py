@@ -425,3 +425,162 @@ def trainer_gpu(rank, world, port, run_dir, total, tag):
                  "train.device=cuda", f"hydra.run.dir={run_dir}/run_{tag}"]
     hc.run_job(lambda cfg: dt.run(cfg, before_teardown=grab), ROOT / "conf", "config", overrides)
     torch.save(dict(captured), os.path.join(run_dir, f"res_{tag}_rank{rank}.pt"))
+
+
+def collectives_stress(rank, world, port, out_dir, max_mb=1024):
+    """SURVEY §4.3 / §5.2 stress tier (stands in for the race checks compute-sanitizer would do): every all-reduce
+    size class from 1 KiB to ``max_mb`` MiB against an NCCL fp32 oracle, launches queued back to back without host
+    synchronisation (flag / sequence reuse across the one-shot and two-shot kernels), and the same collectives while a
+    persistent GEMM burst owns the SMs on another stream, with per-rank random host and device launch skew.
+    Every result must also be bitwise identical on all ranks."""
+    import random
+    import time
+
+    from distributed_training_b200.ops import native
+    from distributed_training_b200.parallel.symm import SymmComm
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world)
+    dev = torch.device("cuda", rank)
+    max_bytes = max_mb << 20
+    comm = SymmComm(dev, segment_bytes=max_bytes + (192 << 20))
+    rng = random.Random(1234 + rank)
+    checked = 0
+
+    def fill(n, dtype, seed):
+        g = torch.Generator(device=dev).manual_seed(seed * 64 + rank)
+        return torch.randn(n, device=dev, generator=g).to(dtype)
+
+    def oracle(x):
+        """Mean over ranks by NCCL in fp32 (bf16 inputs are exact in fp32; fp32 sums differ by summation order only)."""
+        ref = x.float()
+        dist.all_reduce(ref)
+        return ref.div_(world)
+
+    def check(got, ref, what):
+        nonlocal checked
+        tol = 2 ** -7 if got.dtype == torch.bfloat16 else 2e-6
+        diff = (got.float() - ref).abs()
+        bound = tol * ref.abs() + tol * 4
+        assert bool((diff <= bound).all()), (what, float(diff.max()))
+        root = got.clone()
+        dist.broadcast(root, 0)                     # bitwise identical on every rank
+        assert torch.equal(root, got), (what, "ranks disagree bitwise")
+        checked += 1
+
+    try:
+        big = comm.alloc(max_bytes // 2, torch.bfloat16)
+        # ---- A. every size class, idle GPU ----
+        sizes = [1 << 10, (4 << 10) + 32, 64 << 10, (64 << 10) + 16, 1 << 20, (16 << 20) + 4096, 128 << 20, max_bytes]
+        for nbytes in [s for s in sizes if s <= max_bytes]:
+            for dtype in ((torch.bfloat16, torch.float32) if nbytes <= (16 << 20) + 4096 else (torch.bfloat16,)):
+                esize = 2 if dtype == torch.bfloat16 else 4
+                n = nbytes // esize
+                buf = big.view(torch.uint8)[:nbytes].view(dtype)
+                for rep in range(2):
+                    x = fill(n, dtype, nbytes % 9973 + rep)
+                    ref = oracle(x)
+                    buf.copy_(x)
+                    comm.all_reduce_avg_(buf).wait()
+                    check(buf, ref, ("idle", nbytes, str(dtype), rep))
+                    del x, ref
+        # ---- B. back to back, no host synchronisation, mixed kernels ----
+        slot_bytes = [16 << 10, 1 << 20, 48 << 10, (2 << 20) + 64, 1 << 10, 8 << 20, 64 << 10, 512 << 10]
+        slots, offs, o = [], [], 0
+        raw = big.view(torch.uint8)
+        for b in slot_bytes:
+            slots.append(raw[o:o + b].view(torch.bfloat16))
+            o += (b + 255) // 256 * 256
+        for round_ in range(3):
+            xs = [fill(s.numel(), torch.bfloat16, 500 + 10 * round_ + i) for i, s in enumerate(slots)]
+            refs = [oracle(x) for x in xs]
+            for s, x in zip(slots, xs):
+                s.copy_(x)
+            works = [comm.all_reduce_avg_(s) for s in slots]          # 8 launches queued, none waited for
+            works += [comm.all_reduce_avg_(slots[1])]                 # and the mean of a mean on one of them
+            for w_ in works:
+                w_.wait()
+            for i, (s, ref) in enumerate(zip(slots, refs)):
+                check(s, ref, ("back-to-back", round_, i))
+        # ---- C. beside a GEMM burst that owns the SMs, with launch skew ----
+        m, nn, k = 4096, 8192, 8192
+        a = fill(m * k, torch.bfloat16, 7).view(m, k)
+        bmat = fill(nn * k, torch.bfloat16, 8).view(nn, k)
+        out = torch.empty(m, nn, device=dev, dtype=torch.bfloat16)
+        gemm_stream = torch.cuda.Stream(dev)
+        par = comm.alloc((32 << 20) // 2, torch.bfloat16)
+        for it, (nbytes, exclusive) in enumerate([(64 << 10, False), (1 << 20, False), (16 << 20, False),
+                                                  (16 << 20, True), (128 << 20, True), (128 << 20, False),
+                                                  (32 << 20, True), (32 << 20, False)]):
+            if nbytes > max_bytes:
+                continue
+            n = nbytes // 2
+            buf = big[:n]
+            x = fill(n, torch.bfloat16, 900 + it)
+            ref = oracle(x)
+            buf.copy_(x)
+            sgd = nbytes == (32 << 20)
+            if sgd:
+                p0 = fill(n, torch.bfloat16, 77)      # rank 0's draw becomes everybody's parameters
+                dist.broadcast(p0, 0)
+                par[:n].copy_(p0)
+            torch.cuda.synchronize()
+            comm.exclusive_now = exclusive
+            gemm_ctas = 148 - comm.exclusive_sms if exclusive else 0
+            gemm_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(gemm_stream):
+                for _ in range(12):                    # ~4 ms of back-to-back persistent GEMMs
+                    native.gemm(a, bmat, out, m=m, n=nn, k=k, max_ctas=gemm_ctas)
+            time.sleep(rng.uniform(0.0, 2e-3))         # host skew
+            torch.cuda._sleep(int(rng.uniform(0, 1.5e6)))     # device skew on the launching stream (up to ~1 ms)
+            if sgd:
+                comm.all_reduce_sgd_(buf, par[:n], 0.05, 0.01).wait()
+            else:
+                comm.all_reduce_avg_(buf).wait()
+            torch.cuda.current_stream().wait_stream(gemm_stream)
+            if sgd:
+                expect = p0.float() * (1 - 0.05 * 0.01) - 0.05 * ref
+                check(par[:n], expect, ("beside-gemm sgd", nbytes, exclusive))
+                assert torch.equal(buf, x), "fused SGD must leave the gradients alone"
+            else:
+                check(buf, ref, ("beside-gemm", nbytes, exclusive))
+        comm.exclusive_now = False
+        # all-gather and reduce-scatter beside the same burst
+        n = (8 << 20) // 2
+        comm.reserve((world + 2) * n * 2 + 4096)
+        full, shard = comm.alloc(world * n, torch.bfloat16), comm.alloc(n, torch.bfloat16)
+        x = fill(n, torch.bfloat16, 41)
+        shard.copy_(x)
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x)
+        torch.cuda.synchronize()
+        gemm_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(gemm_stream):
+            for _ in range(6):
+                native.gemm(a, bmat, out, m=m, n=nn, k=k)
+        torch.cuda._sleep(int(rng.uniform(0, 1.5e6)))
+        comm.all_gather_into(full, shard)
+        torch.cuda.synchronize()
+        assert torch.equal(full, torch.cat(parts)), "all-gather beside a GEMM"
+        xf = fill(world * n, torch.bfloat16, 43)
+        ref = oracle(xf)[rank * n:(rank + 1) * n]
+        full.copy_(xf)
+        rs_out = torch.empty(n, device=dev)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(gemm_stream):
+            for _ in range(6):
+                native.gemm(a, bmat, out, m=m, n=nn, k=k)
+        time.sleep(rng.uniform(0.0, 2e-3))
+        comm.reduce_scatter_avg_into(rs_out, full)
+        torch.cuda.synchronize()
+        tol = 2 ** -7 if comm.nvls_active else 1e-6
+        assert torch.allclose(rs_out, ref, rtol=tol, atol=tol * 4), "reduce-scatter beside a GEMM"
+        comm.barrier()
+        comm.check_errors()
+        torch.save({"ok": True, "checked": checked, "nvls": comm.nvls_active, "max_mb": max_mb},
+                   os.path.join(out_dir, f"ok{rank}.pt"))
+    finally:
+        comm.close()
+        dist.destroy_process_group()

@@ -27,6 +27,18 @@ def test_collectives_exact_and_bitwise_identical(tmp_path, nvls):
     assert res["nvls"] == (nvls == "1")
 
 
+@pytest.mark.timeout(600)
+def test_collectives_stress_sizes_back_to_back_and_beside_gemm(tmp_path):
+    """1 KiB - 1 GiB against an NCCL fp32 oracle, queued back to back, and beside a GEMM burst with launch skew."""
+    import os
+
+    w = _world()
+    max_mb = int(os.environ.get("DTB_STRESS_MAX_MB", "1024"))
+    mp.spawn(G.collectives_stress, args=(w, free_port(), str(tmp_path), max_mb), nprocs=w, join=True)
+    res = [torch.load(tmp_path / f"ok{r}.pt", weights_only=False) for r in range(w)]
+    assert all(r["ok"] and r["checked"] >= 30 for r in res), res
+
+
 @pytest.mark.timeout(120)
 def test_watchdog_turns_a_missing_peer_into_an_error(tmp_path):
     w = 2

@@ -114,6 +114,26 @@ def test_gemm_dgelu_and_axpby_epilogues_fp32_out():
     assert torch.allclose(res, 0.5 * (dy.float() @ w.float()) + 2 * acc, atol=0.05, rtol=1e-2)
 
 
+@pytest.mark.parametrize("m,n,k,cta_pair", [(512, 1024, 4096, 0), (300, 520, 2048, 0), (4096, 2048, 4096, 2),
+                                              (640, 768, 256, 1)])
+def test_gemm_colsum_in_the_epilogue(m, n, k, cta_pair):
+    """dgrad * gelu'(z) with the bias gradient (column sums of the bf16 output) added from the epilogue."""
+    dy, w = _bf16(m, k, seed=31), _bf16(k, n, scale=1.0 / math.sqrt(k), seed=32)
+    zprev = _bf16(m, n, seed=33)
+    out = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+    cs = torch.zeros(n, device=DEV)
+    for rep in range(2):                       # the second call must ADD to the first
+        native.gemm(dy, w, out, m=m, n=n, k=k, b_mn=True, aux=zprev, act=2, colsum=cs, cta_pair=cta_pair)
+    ref_out = torch.empty_like(out)
+    native.gemm(dy, w, ref_out, m=m, n=n, k=k, b_mn=True, aux=zprev, act=2, cta_pair=cta_pair)
+    assert torch.equal(out, ref_out)
+    want = 2 * out.float().sum(0)
+    assert torch.allclose(cs, want, rtol=1e-4, atol=1e-3 * math.sqrt(m)), (cs - want).abs().max().item()
+    grad = torch.empty(n, dtype=torch.bfloat16, device=DEV)
+    native.take_f32_to_bf16(cs, grad)
+    assert torch.allclose(grad.float(), want, rtol=2 ** -7, atol=1e-2) and float(cs.abs().max()) == 0.0
+
+
 def test_gemm_batched_strided_heads():
     # attention-style: per (batch, head) problem carved out of a packed [B, T, 3C] tensor
     B, T, H, D = 2, 256, 3, 64
@@ -254,16 +274,27 @@ def test_layernorm_bwd_bf16_param_grads_match_fp32_path():
 def test_cross_entropy_fused(rows, vocab, ld):
     logits = _bf16(rows, ld, scale=2.0, seed=1)
     targets = torch.randint(0, vocab, (rows,), device=DEV)
+    logits[0, targets[0]] = 14.0          # a confident row: p_t -> 1, the gradient p_t - 1 must not lose its digits
+    logits[1, targets[1]] = 9.0
+    targets[2] = -100                      # ignore_index: zero loss, zero gradient
     ref_in = logits[:, :vocab].float().requires_grad_(True)
     ref_loss = F.cross_entropy(ref_in, targets, reduction="none")
-    ref_loss.mean().backward()
+    (ref_loss.sum() / rows).backward()
     row_loss = torch.empty(rows, device=DEV)
     work = logits.clone()
     native.cross_entropy_fwd_bwd(work, targets, row_loss, vocab, 1.0 / rows)
     assert torch.allclose(row_loss, ref_loss, atol=2e-3, rtol=1e-3)
     assert torch.allclose(work[:, :vocab].float(), ref_in.grad, atol=2e-3 / rows + 1e-5, rtol=2e-2)
+    for r in (0, 1):                       # relative accuracy of the target column itself
+        got, want = float(work[r, targets[r]]), float(ref_in.grad[r, targets[r]])
+        assert abs(got - want) <= 1e-2 * abs(want) + 1e-9, (r, got, want)
+    assert float(work[2].float().abs().max()) == 0.0 and float(row_loss[2]) == 0.0
     if ld > vocab:
         assert float(work[:, vocab:].float().abs().max()) == 0.0
+    # loss only (no gradient): the logits must be left untouched
+    work2 = logits.clone()
+    native.cross_entropy_fwd_bwd(work2, targets, row_loss, vocab, 1.0 / rows, write_grad=False)
+    assert torch.equal(work2, logits) and torch.allclose(row_loss, ref_loss, atol=2e-3, rtol=1e-3)
 
 
 def test_soft_cross_entropy_and_mse():
