@@ -125,8 +125,8 @@ def test_gemm_colsum_in_the_epilogue(m, n, k, cta_pair):
     for rep in range(2):                       # the second call must ADD to the first
         native.gemm(dy, w, out, m=m, n=n, k=k, b_mn=True, aux=zprev, act=2, colsum=cs, cta_pair=cta_pair)
     ref_out = torch.empty_like(out)
-    native.gemm(dy, w, ref_out, m=m, n=n, k=k, b_mn=True, aux=zprev, act=2, cta_pair=cta_pair)
-    assert torch.equal(out, ref_out)
+    native.gemm(dy, w, ref_out, m=m, n=n, k=k, b_mn=True, aux=zprev, act=2, cta_pair=cta_pair, split_k=1)
+    assert torch.equal(out, ref_out)          # same kernel, same tile walk: the option must not change D
     want = 2 * out.float().sum(0)
     assert torch.allclose(cs, want, rtol=1e-4, atol=1e-3 * math.sqrt(m)), (cs - want).abs().max().item()
     grad = torch.empty(n, dtype=torch.bfloat16, device=DEV)
