@@ -58,7 +58,9 @@ def parse_args():
     ap.add_argument("--config", choices=list(CONFIGS), default="wide_mlp")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (weak scaling); 0 = the config's")
     ap.add_argument("--layers", type=int, default=0, help="gpt2 configs: override n_layer (smoke runs only)")
-    ap.add_argument("--lr", type=float, default=1e-4)
+    ap.add_argument("--lr", type=float, default=0.0,
+                    help="0 = the config's (SGD 0.05: large enough that bf16 weights move every step, so the loss "
+                         "after K steps depends on the gradients every rank contributed; AdamW 1e-4)")
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--depth", type=int, default=DEPTH)
     ap.add_argument("--comm-ctas", type=int, default=0)
@@ -71,6 +73,8 @@ def parse_args():
     if args.batch:
         args.cfg["batch"] = args.batch
     args.batch = args.cfg["batch"]
+    if not args.lr:
+        args.lr = 0.05 if args.cfg["optimizer"] == "sgd" else 1e-4
     if args.layers and args.cfg["kind"] == "gpt2":
         args.cfg["n_layer"] = args.layers
     return args

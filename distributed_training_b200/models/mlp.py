@@ -22,6 +22,8 @@ from torch import nn
 from ..ops import native
 
 _FUSED_COLSUM = os.environ.get("DTB_FUSED_COLSUM", "1") != "0"
+#: weight gradients on a side stream so that consecutive GEMMs fill each other's last wave (DTB_ASYNC_WGRAD=0: one stream)
+_ASYNC_WGRAD = os.environ.get("DTB_ASYNC_WGRAD", "1") != "0"
 
 
 class MLP(nn.Module):
@@ -69,14 +71,25 @@ class MLP(nn.Module):
                 "z": [torch.empty(rows, self.dims[i + 1], **bf) for i in range(n - 1)],   # pre-activations
                 "h": [torch.empty(rows, self.dims[i + 1], **bf) for i in range(n - 1)],   # activations
                 "logits": torch.empty(rows, self.dims[-1], **bf),
-                "dz": [torch.empty(rows, max(self.dims[1:-1] or [8]), **bf) for _ in range(2)],
+                # output gradients: D_i writes slot i % 3 while W_{i+1} (side stream) may still read slot (i+2) % 3
+                "dz": [torch.empty(rows, max(self.dims[1:-1] or [8]), **bf) for _ in range(3 if n > 2 else 2)],
                 "row_loss": torch.empty(rows, dtype=torch.float32, device=device),
                 "loss": torch.empty((), dtype=torch.float32, device=device),
                 # fp32 bias-gradient accumulators the dgrad epilogues add into (zero between steps)
                 "bsum": [torch.zeros(self.dims[i + 1], dtype=torch.float32, device=device) for i in range(n - 1)],
             }
+            if device.type == "cuda":
+                ws["ev_d"] = [torch.cuda.Event() for _ in range(n)]      # dz_i complete (dgrad stream)
+                ws["ev_w"] = [torch.cuda.Event() for _ in range(n)]      # layer i's gradients queued (wgrad stream)
             self._ws = {key: ws}      # one live batch shape at a time
         return ws
+
+    def _wgrad_stream(self, device: torch.device) -> "torch.cuda.Stream":
+        st = getattr(self, "_side_stream", None)
+        if st is None or st.device != device:
+            st = torch.cuda.Stream(device)
+            self._side_stream = st
+        return st
 
     def _fuse_bias_grad(self, i: int, k_of_dgrad: int) -> bool:
         """Layer ``i``'s bias gradient comes out of the epilogue of the dgrad GEMM that produces its output gradient
@@ -134,63 +147,104 @@ class MLP(nn.Module):
         # ---- loss + dlogits in place
         native.cross_entropy_fwd_bwd(ws["logits"], targets, ws["row_loss"], self.dims[-1], 1.0 / rows)
         native.mean_f32(ws["row_loss"], ws["loss"])
-        # ---- backward, last layer first; each layer's grads go to the reducer as soon as queued
+        # ---- backward, last layer first; each layer's grads go to the reducer as soon as queued.
+        # Two streams: the dgrad chain (D_i: dz_i -> dz_{i-1}) stays on the caller's stream, the weight gradients
+        # (W_i: needs dz_i only) go to a side stream.  A persistent GEMM ends with a partly filled wave -- 512 tiles
+        # over the 72 CTA pairs that are left while 4 SMs carry the gradient reduction are 7.1 waves, i.e. 8 -- and
+        # on ONE stream the next kernel cannot start before the last CTA has exited.  With two independent GEMMs
+        # queued the SMs a finishing kernel frees are taken by the other one's CTAs (the tile scheduler is a global
+        # counter per stream, so late CTAs simply join).
+        async_w = (_ASYNC_WGRAD and x.is_cuda
+                   and (grad_sink is None or getattr(grad_sink, "supports_async_wgrad", False)))
+        main = torch.cuda.current_stream() if async_w else None
+        side = self._wgrad_stream(x.device) if async_w else None
+        nbuf = len(ws["dz"]) if async_w else 2
         dz = ws["logits"]
         cap = max_ctas
+        ev_dz = None            # dz_i (and layer i's bias-gradient sums) are complete on the dgrad stream
+        if async_w:
+            ev_dz = ws["ev_d"][n - 1]
+            ev_dz.record(main)
         for i in range(n - 1, -1, -1):
             layer = self.layers[i]
             out_f, in_f = layer.weight.shape
             h_in = x if i == 0 else ws["h"][i - 1]
             nxt = None
+            ev_next = None
             if i > 0:
                 # dgrad fused with GELU': dz_prev = (dz W_i) * gelu'(z_{i-1}).  It runs BEFORE this layer's
                 # wgrad is handed to the reducer: a fused reduce+SGD (or the fused epilogue below) overwrites W_i.
                 # The same epilogue adds dz_prev's column sums (= the bias gradient of layer i-1) to an fp32
                 # accumulator: no separate pass over dz_prev.
-                nxt = ws["dz"][i % 2]
+                nxt = ws["dz"][i % nbuf]
+                if async_w and i + nbuf - 1 <= n - 1:
+                    main.wait_event(ws["ev_w"][i + nbuf - 1])      # the wgrad that read this buffer's last content
                 fuse_bias = self._fuse_bias_grad(i - 1, out_f)
                 native.gemm(dz, wv(layer.weight), nxt, m=rows, n=in_f, k=out_f, b_mn=True, lda=dz.shape[1], ldb=in_f,
                             ldd=nxt.shape[1], aux=ws["z"][i - 1], ld_aux=in_f, act=2, max_ctas=cap,
                             colsum=ws["bsum"][i - 1] if fuse_bias else None)
-            if fused_sgd is not None:
-                # single replica: W = (1 - lr*wd) W - lr * (dz^T h_in), applied in the wgrad epilogue (no dW in HBM)
-                lr, wd = fused_sgd
-                native.gemm(dz, h_in, layer.weight.data, m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
-                            lda=dz.shape[1], ldb=in_f, aux=layer.weight.data, alpha=-lr, beta=1.0 - lr * wd,
-                            max_ctas=cap)
-                if on_updated is not None:
-                    on_updated([layer.weight])
-            elif i == 0 and getattr(grad_sink, "tail_chunks", lambda p: 1)(layer.weight) > 1:
-                # the last wgrad of backward: produce (and reduce) it in row chunks so that only the final
-                # chunk's reduction is exposed
-                nch = grad_sink.tail_chunks(layer.weight)
-                gw, per = grad_of(layer.weight), out_f // nch
-                for c in range(nch):
-                    native.gemm(dz[:, c * per:], h_in, gw[c * per:], m=per, n=in_f, k=rows, a_mn=True, b_mn=True,
-                                lda=dz.shape[1], ldb=in_f, max_ctas=cap)
-                    grad_sink.mark_ready_chunk(layer.weight, c, nch)
-            else:
-                # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major), straight into the gradient bucket
-                native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
-                            lda=dz.shape[1], ldb=in_f, max_ctas=cap)
-            if layer.bias is not None:
-                if i < n - 1 and self._fuse_bias_grad(i, self.dims[i + 2]):
-                    gb = grad_of(layer.bias)
-                    if gb.dtype == torch.bfloat16:
-                        native.take_f32_to_bf16(ws["bsum"][i], gb)
-                    else:
-                        gb.copy_(ws["bsum"][i])
-                        ws["bsum"][i].zero_()
+                if async_w:
+                    ev_next = ws["ev_d"][i - 1]
+                    ev_next.record(main)
+            if async_w:
+                side.wait_event(ev_dz)
+                if fused_sgd is not None and ev_next is not None:
+                    side.wait_event(ev_next)         # the epilogue below rewrites W_i, which D_i is reading
+                torch.cuda.set_stream(side)
+            try:
+                if fused_sgd is not None:
+                    # single replica: W = (1 - lr*wd) W - lr * (dz^T h_in), applied in the wgrad epilogue (no dW in HBM)
+                    lr, wd = fused_sgd
+                    native.gemm(dz, h_in, layer.weight.data, m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
+                                lda=dz.shape[1], ldb=in_f, aux=layer.weight.data, alpha=-lr, beta=1.0 - lr * wd,
+                                max_ctas=cap)
+                    if on_updated is not None:
+                        on_updated([layer.weight])
+                elif (i < getattr(grad_sink, "TAIL_LAYERS", 1)
+                      and getattr(grad_sink, "tail_chunks", lambda p: 1)(layer.weight) > 1):
+                    # the last wgrads of backward: produce (and reduce) them in row chunks so that only the final
+                    # chunk's reduction is exposed; the reductions get more SMs here and the GEMM pieces leave them
+                    nch = grad_sink.tail_chunks(layer.weight)
+                    gw, per = grad_of(layer.weight), out_f // nch
+                    if hasattr(grad_sink, "begin_tail"):
+                        grad_sink.begin_tail()
+                        cap = grad_sink.tail_gemm_ctas(cap)
+                    for c in range(nch):
+                        native.gemm(dz[:, c * per:], h_in, gw[c * per:], m=per, n=in_f, k=rows, a_mn=True, b_mn=True,
+                                    lda=dz.shape[1], ldb=in_f, max_ctas=cap)
+                        grad_sink.mark_ready_chunk(layer.weight, c, nch)
                 else:
-                    native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
-            if grad_sink is not None:
-                grad_sink.mark_ready(layer.weight)
+                    # wgrad: dW[out,in] = dz^T h_in   (both operands MN-major), straight into the gradient bucket
+                    native.gemm(dz, h_in, grad_of(layer.weight), m=out_f, n=in_f, k=rows, a_mn=True, b_mn=True,
+                                lda=dz.shape[1], ldb=in_f, max_ctas=cap)
                 if layer.bias is not None:
-                    grad_sink.mark_ready(layer.bias)
-                if bwd_max_ctas:
-                    cap = bwd_max_ctas
+                    if i < n - 1 and self._fuse_bias_grad(i, self.dims[i + 2]):
+                        gb = grad_of(layer.bias)
+                        if gb.dtype == torch.bfloat16:
+                            native.take_f32_to_bf16(ws["bsum"][i], gb)
+                        else:
+                            gb.copy_(ws["bsum"][i])
+                            ws["bsum"][i].zero_()
+                    else:
+                        native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
+                if grad_sink is not None:
+                    if async_w and ev_next is not None:
+                        side.wait_event(ev_next)     # the reducer may rewrite W_i (fused reduce + SGD): D_i must be done
+                    grad_sink.mark_ready(layer.weight)
+                    if layer.bias is not None:
+                        grad_sink.mark_ready(layer.bias)
+                    if bwd_max_ctas:
+                        cap = bwd_max_ctas
+                if async_w:
+                    ws["ev_w"][i].record(side)
+            finally:
+                if async_w:
+                    torch.cuda.set_stream(main)
             if nxt is not None:
                 dz = nxt
+                ev_dz = ev_next
+        if async_w:
+            main.wait_stream(side)
         return ws["loss"]
 
 

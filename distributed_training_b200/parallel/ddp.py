@@ -73,6 +73,16 @@ class ReplicatedModule(nn.Module):
     (SURVEY §5.4).
     """
 
+    @property
+    def supports_async_wgrad(self) -> bool:
+        """``grad_view`` / ``mark_ready`` may be called with a side stream current (the native MLP can queue its
+        weight gradients there; the reduction is ordered behind whatever stream is current at the call).  Used with
+        one replica only: with two GEMMs always queued, the SMs the backward GEMMs leave to the whole-SM reduction
+        CTAs are taken by the other GEMM's waiting CTAs, and the reductions then start only when a persistent GEMM
+        ends (4 GPUs, profiles/timeline_wide_mlp_n4_async_x8.json: 128 MiB reductions 0.9-1.15 ms instead of 0.48,
+        1.35 ms of them after the last GEMM).  DTB_ASYNC_WGRAD_MULTI=1 turns it on regardless."""
+        return self.comm.world_size == 1 or os.environ.get("DTB_ASYNC_WGRAD_MULTI", "0") == "1"
+
     def __init__(self, module: nn.Module, comm: Communicator, bucket_cap_mb: float = 25.0,
                  first_bucket_mb: float = 1.0, init_sync: bool = True,
                  grad_dtype: Optional[torch.dtype] = None) -> None:
@@ -259,8 +269,33 @@ class ReplicatedModule(nn.Module):
 
     #: weights smaller than this are reduced in one piece even when they end backward
     TAIL_CHUNK_MIN_BYTES = 32 << 20
-    #: pieces the last weight gradient of backward is produced (and reduced) in; DTB_DDP_TAIL_CHUNKS overrides
-    TAIL_CHUNKS = int(os.environ.get("DTB_DDP_TAIL_CHUNKS", "8"))
+    #: pieces a weight gradient at the end of backward is produced (and reduced) in; DTB_DDP_TAIL_CHUNKS overrides.
+    #: Device timeline at 4 GPUs (profiles/timeline_wide_mlp_n4_sync_x4.json): with only the LAST wgrad cut in 8, the
+    #: bucket before it was still reduced in one piece after its GEMM (0.47 ms) and the eight 16 MiB pieces queued up
+    #: behind it at 78 us each: 0.52 ms of reduction after the last GEMM.  Eight 1024-row GEMMs also took 0.57 ms
+    #: where the whole wgrad takes 0.36 (128 tiles on 72 CTA pairs = two waves each).  Four 2048-row pieces for each
+    #: of the last TAIL_LAYERS layers: the pieces are 4 full waves on 66 pairs and every reduction but the last one
+    #: runs under a GEMM.
+    TAIL_CHUNKS = int(os.environ.get("DTB_DDP_TAIL_CHUNKS", "4"))
+    #: how many layers at the end of backward get that treatment (DTB_DDP_TAIL_LAYERS)
+    TAIL_LAYERS = int(os.environ.get("DTB_DDP_TAIL_LAYERS", "2"))
+    #: whole-SM CTAs of the reductions in the tail (DTB_DDP_TAIL_SMS): the GEMM pieces there leave that many SMs free
+    #: (``tail_gemm_ctas``) at no cost in waves, and nothing hides a slow reduction any more
+    TAIL_SMS = int(os.environ.get("DTB_DDP_TAIL_SMS", "16"))
+
+    def begin_tail(self) -> None:
+        """Called by a native model before the first chunked weight gradient: from here on the reductions are on the
+        critical path, so they get ``TAIL_SMS`` whole SMs instead of ``exclusive_sms``."""
+        if getattr(self.comm, "exclusive_now", False) and self.TAIL_SMS > int(getattr(self.comm, "exclusive_sms", 0)):
+            self.comm.exclusive_boost = self.TAIL_SMS
+
+    def tail_gemm_ctas(self, cap: int) -> int:
+        """CTA cap for the GEMM pieces of the tail (leaves ``TAIL_SMS`` SMs to the reductions)."""
+        if not getattr(self.comm, "exclusive_boost", 0):
+            return cap
+        sms = torch.cuda.get_device_properties(self.comm.device).multi_processor_count
+        want = max(2, (sms - self.comm.exclusive_boost) & ~1)
+        return min(cap, want) if cap else want
 
     def tail_chunks(self, param: nn.Parameter) -> int:
         """How many row chunks the *last* weight gradient of backward should be produced in.  Its reduction
@@ -323,6 +358,7 @@ class ReplicatedModule(nn.Module):
             self._in_manual_step = False
             if hasattr(self.comm, "exclusive_now"):
                 self.comm.exclusive_now = False
+                self.comm.exclusive_boost = 0
         return loss
 
     def finish_gradient_sync(self) -> None:

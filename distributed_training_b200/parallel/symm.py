@@ -160,6 +160,8 @@ class SymmComm(Communicator):
         self._exclusive_from_env = env_excl is not None
         self.exclusive_min_bytes = 8 << 20
         self.exclusive_now = False     # set by the data-parallel wrapper while a step that left SMs free is running
+        #: > 0: SM count that replaces ``exclusive_sms`` for the reductions at the end of backward (set by the wrapper)
+        self.exclusive_boost = 0
         #: opt-in (DTB_COMM_CE=1): large bf16 all-reduces move their NVLink legs with the copy engines
         #: (dtb_comm_all_reduce_ce).  Local DMA traffic barely slows a GEMM, but measured at 2 GPUs the peer copies ran
         #: at ~1/3 of their solo rate beside the GEMMs and the step was 0.4 ms slower than with co-resident comm CTAs
@@ -450,7 +452,7 @@ class SymmComm(Communicator):
 
     def _ctas_for(self, nbytes: int) -> int:
         if self.exclusive_sms > 0 and self.exclusive_now and nbytes >= self.exclusive_min_bytes:
-            return self.exclusive_sms | native.EXCLUSIVE
+            return (self.exclusive_boost or self.exclusive_sms) | native.EXCLUSIVE
         return self.comm_ctas
 
     def _ce_scratch(self, nbytes: int) -> Optional[torch.Tensor]:

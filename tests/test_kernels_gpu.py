@@ -390,6 +390,32 @@ def test_native_mlp_step_matches_autograd():
         assert (g - p.grad).abs().max().item() <= 0.06 * scale + 1e-4
 
 
+def test_native_mlp_two_stream_backward_matches_one_stream(monkeypatch):
+    """Weight gradients on the side stream (tails of consecutive GEMMs overlap) must give what the one-stream order
+    gives: bit-identical weight gradients and loss, bias gradients equal up to the order of the fp32 reductions."""
+    from distributed_training_b200.models import mlp as mlp_mod
+
+    torch.manual_seed(3)
+    model = mlp_mod.MLP(2048, 2048, 2048, num_layers=5, dtype=torch.bfloat16).to(DEV)
+    x = _bf16(2048, 2048, seed=41)
+    y = torch.randint(0, 2048, (2048,), device=DEV)
+    results = []
+    for flag in (False, True, True):
+        monkeypatch.setattr(mlp_mod, "_ASYNC_WGRAD", flag)
+        for p in model.parameters():
+            p.grad = None
+        loss = model.forward_backward(x, y)
+        torch.cuda.synchronize()
+        results.append((float(loss), [p.grad.clone() for p in model.parameters()]))
+    for loss, grads in results[1:]:
+        assert loss == results[0][0]
+        for p, g, g0 in zip(model.parameters(), grads, results[0][1]):
+            if p.dim() == 2:
+                assert torch.equal(g, g0)
+            else:
+                assert torch.allclose(g.float(), g0.float(), rtol=2 ** -6, atol=1e-3)
+
+
 def test_launch_counter_counts():
     native.reset_launch_count()
     x = _bf16(1024, seed=1)
