@@ -303,6 +303,250 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restric
   }
 }
 
+// 32 score columns (chunk cc of a 128-column row) of one query row: maximum, and exponentials against a given reference
+// written to the P tile.  DIAG = the tile on the causal diagonal (column <= row only); every other tile takes the
+// unmasked instantiation (a per-element predicate on all tiles cost 40 % of the forward's instructions).
+template <bool DIAG>
+__device__ __forceinline__ float chunk_max(const uint32_t (&x)[32], int cc, int row) {
+  // four independent chains: a single 32-deep fmax chain showed up as fixed-latency ("wait") stalls with only two
+  // warps per scheduler
+  float v[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int e = 0; e < 32; ++e)
+    if (!DIAG || cc * 32 + e <= row) v[e & 3] = fmaxf(v[e & 3], __uint_as_float(x[e]));
+  return fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
+}
+template <bool DIAG>
+__device__ __forceinline__ float chunk_exp(const uint32_t (&x)[32], int cc, int row, float c, float mc, uint8_t* sP) {
+  float rowsum = 0.f;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float p[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float v = fast_exp2(fmaf(__uint_as_float(x[q * 8 + e]), c, -mc));
+      p[e] = (!DIAG || cc * 32 + q * 8 + e <= row) ? v : 0.f;
+    }
+    rowsum += ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]));
+    uint4 pk;
+    pk.x = pack2(p[0], p[1]);
+    pk.y = pack2(p[2], p[3]);
+    pk.z = pack2(p[4], p[5]);
+    pk.w = pack2(p[6], p[7]);
+    *reinterpret_cast<uint4*>(sP + swz_chunk(row, cc * 4 + q)) = pk;
+  }
+  return rowsum;
+}
+
+// Same decomposition with O resident in TMEM (P V accumulates there) and lazy rescaling: per tile one mbarrier wait and
+// one __syncthreads, no TMEM read-back of O (it cost 512 of the ~1500 TMEM-read cycles per tile at 64 B/clk) and no
+// 64 FMAs per thread; the row maximum that P is taken against is refreshed only when it would grow by more than 2^8.
+__global__ void __launch_bounds__(128, 2)
+fwd_lazy_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, float* __restrict__ lse,
+           int T, int H, float scale) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + TILE_BYTES;            // 2 stages
+  uint8_t* sV = sK + 2 * TILE_BYTES;        // single buffer: reloaded once P V of the previous tile is done
+  uint8_t* sP = sV + TILE_BYTES;            // [128 x 128] bf16
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * TILE_BYTES);
+  uint64_t* q_full = bars;
+  uint64_t* k_full = bars + 1;              // [2]
+  uint64_t* v_full = bars + 3;
+  uint64_t* s_done = bars + 4;
+  uint64_t* pv_done = bars + 5;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 6);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  // Longest-processing-time-first over the whole grid: CTAs are dispatched in linear order, so a 1-D grid whose first
+  // B*H blocks are the longest query rows (n_kv = T/128 tiles), the next B*H the second longest, ... keeps the SMs
+  // evenly loaded to the end.  With the (q-tile, head, batch) grid the causal 8,7,...,1 pattern repeated per head and
+  // the kernel ran 20 tile-times where the average load is 14 (simulated; 47.5 us measured).
+  const int n_bh = gridDim.x / (T / TQ);
+  const int qt = T / TQ - 1 - static_cast<int>(blockIdx.x) / n_bh;
+  const int bh = static_cast<int>(blockIdx.x) % n_bh;
+  const int h = bh % H, b = bh / H;
+  const int C = H * HD;
+  const int n_kv = qt + 1;
+  const int row_base = b * T;
+
+  if (tid == 0) {
+    prefetch_tensormap(&map_qkv);
+    mbar_init(q_full, 1);
+    mbar_init(&k_full[0], 1);
+    mbar_init(&k_full[1], 1);
+    mbar_init(v_full, 1);
+    mbar_init(s_done, 1);
+    mbar_init(pv_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<1>(tmem_ptr, 256);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+
+  if (tid == 0) {
+    mbar_arrive_expect_tx(q_full, TILE_BYTES);
+    tma_load_4d(sQ, &map_qkv, q_full, h * HD, row_base + qt * TQ, 0, 0);
+    mbar_arrive_expect_tx(&k_full[0], TILE_BYTES);
+    tma_load_4d(sK, &map_qkv, &k_full[0], C + h * HD, row_base, 0, 0);
+    mbar_arrive_expect_tx(v_full, TILE_BYTES);
+    tma_load_4d(sV, &map_qkv, v_full, 2 * C + h * HD, row_base, 0, 0);
+  }
+
+  const float c = scale * LOG2E;
+  float m = -INFINITY, l = 0.f;
+
+  const uint32_t q_lo = desc_lo(smem_u32(sQ), 16);
+  const uint32_t p_lo = desc_lo(smem_u32(sP), 16);
+  const uint32_t v_lo = desc_lo(smem_u32(sV), 8192);
+  // Prologue: S of tile 0.
+  if (warp == 0) {
+    mbar_wait(q_full, 0);
+    mbar_wait(&k_full[0], 0);
+    tcgen05_fence_after();
+    const uint32_t k_lo = desc_lo(smem_u32(sK), 16);
+    if (elect_one()) {
+      if (n_kv > 1) {
+        mbar_arrive_expect_tx(&k_full[1], TILE_BYTES);
+        tma_load_4d(sK + TILE_BYTES, &map_qkv, &k_full[1], C + h * HD, row_base + TK, 0, 0);
+      }
+#pragma unroll
+      for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(q_lo, k), desc_k(k_lo, k), IDESC_S, k > 0);
+      umma_commit(s_done);
+    }
+    __syncwarp();
+  }
+  for (int j = 0; j < n_kv; ++j) {
+    const int st = j & 1;
+    const bool more = (j + 1 < n_kv);
+    mbar_wait(s_done, j & 1);
+    tcgen05_fence_after();
+    // tcgen05.mma ops of one thread complete in issue order: S of tile j done means P V of tile j-1 (issued before it)
+    // is done too, so V's buffer, the P buffer and K stage `st` (read by S of tile j) are free from here on.
+    if (warp == 0) {
+      if (elect_one()) {
+        if (j > 0) {
+          mbar_arrive_expect_tx(v_full, TILE_BYTES);
+          tma_load_4d(sV, &map_qkv, v_full, 2 * C + h * HD, row_base + j * TK, 0, 0);
+        }
+        if (j + 2 < n_kv) {
+          mbar_arrive_expect_tx(&k_full[st], TILE_BYTES);
+          tma_load_4d(sK + st * TILE_BYTES, &map_qkv, &k_full[st], C + h * HD, row_base + (j + 2) * TK, 0, 0);
+        }
+      }
+      __syncwarp();
+    }
+    uint32_t sv[128];
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t(&chunk)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sv[cc * 32]);
+      tmem_ld_32x32b_x32(tmem_row + cc * 32, chunk);
+    }
+    tmem_ld_wait();
+    const bool diag = (j == qt);
+    float tile_max = -INFINITY;
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      const uint32_t(&chunk)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&sv[cc * 32]);
+      tile_max = fmaxf(tile_max, diag ? chunk_max<true>(chunk, cc, tid) : chunk_max<false>(chunk, cc, tid));
+    }
+    // Lazy rescaling: O stays in TMEM and P V accumulates into it; the reference maximum of a row moves only when the
+    // new maximum is more than 2^8 above it (P then stays below 256: exact enough in bf16, far from fp32 overflow),
+    // so after the first tiles the read-scale-write of O is almost never taken.
+    // Tried on top of this and slower at B8 H12 T1024 (43.1 us for this version): exponentials against the stale
+    // maximum chunk by chunk under the next chunk's tcgen05.ld (47.1: four tcgen05.wait::ld per tile); S of tile j+1
+    // issued right after the score read, before this tile's exponentials, with a second __syncthreads (46.1).
+    const float m_new = fmaxf(m, tile_max);
+    const bool need = (m_new - m) * c > 8.f;       // true on the first tile (m = -inf)
+    float alpha = 1.f;
+    if (need) {
+      alpha = fast_exp2((m - m_new) * c);          // 0 on the first tile
+      m = m_new;
+    }
+    if (j > 0 && __any_sync(0xffffffffu, need)) {
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) {
+        uint32_t ov[16];
+        tmem_ld_32x32b_x16(tmem_row + 128 + cc * 16, ov);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
+        tmem_st_32x32b_x16(tmem_row + 128 + cc * 16, ov);
+      }
+      tmem_st_wait();
+    }
+    const float mc = m * c;
+    float rowsum = 0.f;
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      const uint32_t(&chunk)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&sv[cc * 32]);
+      rowsum += diag ? chunk_exp<true>(chunk, cc, tid, c, mc, sP) : chunk_exp<false>(chunk, cc, tid, c, mc, sP);
+    }
+    l = l * alpha + rowsum;
+    fence_proxy_async_smem();
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+      mbar_wait(v_full, j & 1);
+      if (more) mbar_wait(&k_full[st ^ 1], ((j + 1) >> 1) & 1);
+      tcgen05_fence_after();
+      const uint32_t kn_lo = desc_lo(smem_u32(sK + (st ^ 1) * TILE_BYTES), 16);
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < TK / 16; ++k)
+          umma_f16<1>(tmem_base + 128, desc_k2(p_lo, k), desc_mn(v_lo, k), IDESC_PV, (k > 0) || (j > 0));
+        if (more) {   // every thread has read S of tile j (the __syncthreads above): its TMEM columns are free
+#pragma unroll
+          for (int k = 0; k < HD / 16; ++k) umma_f16<1>(tmem_base, desc_k(q_lo, k), desc_k(kn_lo, k), IDESC_S, k > 0);
+          umma_commit(s_done);
+        } else {
+          umma_commit(pv_done);
+        }
+      }
+      __syncwarp();
+    }
+  }
+  mbar_wait(pv_done, 0);
+  tcgen05_fence_after();
+  float o[HD];
+  {
+    uint32_t ov[64];
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      uint32_t(&chunk)[32] = *reinterpret_cast<uint32_t(*)[32]>(&ov[cc * 32]);
+      tmem_ld_32x32b_x32(tmem_row + 128 + cc * 32, chunk);
+    }
+    tmem_ld_wait();
+#pragma unroll
+    for (int e = 0; e < 64; ++e) o[e] = __uint_as_float(ov[e]);
+  }
+  tcgen05_fence_before();
+
+  const float inv = 1.f / l;
+  const long long grow = static_cast<long long>(row_base + qt * TQ + tid);
+  __nv_bfloat16* op = out + grow * C + h * HD;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    uint4 pk;
+    pk.x = pack2(o[8 * q + 0] * inv, o[8 * q + 1] * inv);
+    pk.y = pack2(o[8 * q + 2] * inv, o[8 * q + 3] * inv);
+    pk.z = pack2(o[8 * q + 4] * inv, o[8 * q + 5] * inv);
+    pk.w = pack2(o[8 * q + 6] * inv, o[8 * q + 7] * inv);
+    *reinterpret_cast<uint4*>(op + 8 * q) = pk;
+  }
+  lse[(static_cast<long long>(b) * H + h) * T + qt * TQ + tid] = m * scale + logf(l);
+
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc<1>(tmem_base, 256);
+  }
+}
+
 // -------------------------------------------------------------------------- backward
 // delta[b,h,t] = sum_d dO * O.  Eight lanes own one (b,t,h) row of 64 elements (16 bytes each), so a warp covers four
 // consecutive heads of a token with fully coalesced 512-byte requests and three shuffle steps (the first version used
@@ -895,11 +1139,18 @@ extern "C" int dtb_attention_fwd(const void* qkv, void* out, float* lse, int bat
   static bool configured = false;
   if (!configured) {
     DTB_CUDA_OK(cudaFuncSetAttribute(fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    DTB_CUDA_OK(cudaFuncSetAttribute(fwd_lazy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
     configured = true;
   }
   dim3 grid(static_cast<unsigned>(seq / TQ) * heads * batch);
-  fwd_kernel<<<grid, 128, FWD_SMEM, static_cast<cudaStream_t>(stream)>>>(map, static_cast<__nv_bfloat16*>(out), lse, seq,
-                                                                         heads, 1.0f / sqrtf(static_cast<float>(HD)));
+  // DTB_ATTN_FWD_LAZY=0: the first kernel (O accumulated in registers, rescaled every tile)
+  static const bool lazy = [] { const char* e = getenv("DTB_ATTN_FWD_LAZY"); return !(e && e[0] == '0'); }();
+  if (lazy)
+    fwd_lazy_kernel<<<grid, 128, FWD_SMEM, static_cast<cudaStream_t>(stream)>>>(
+        map, static_cast<__nv_bfloat16*>(out), lse, seq, heads, 1.0f / sqrtf(static_cast<float>(HD)));
+  else
+    fwd_kernel<<<grid, 128, FWD_SMEM, static_cast<cudaStream_t>(stream)>>>(
+        map, static_cast<__nv_bfloat16*>(out), lse, seq, heads, 1.0f / sqrtf(static_cast<float>(HD)));
   DTB_LAUNCH_OK();
   return 0;
 }

@@ -21,12 +21,24 @@ The reference has no transformer; the baseline for this path is eag
 """
 from __future__ import annotations
 
+import os
 from typing import Any, Dict
 
 import torch
 from torch import nn
 
 from ..ops import native
+
+#: weight gradients on a side stream beside their dgrad (DTB_ASYNC_WGRAD=0: one stream)
+_ASYNC_WGRAD = os.environ.get("DTB_ASYNC_WGRAD", "1") != "0"
+
+
+def _side_stream(model, device: torch.device) -> "torch.cuda.Stream":
+    st = getattr(model, "_wgrad_stream", None)
+    if st is None or st.device != device:
+        st = torch.cuda.Stream(device)
+        model._wgrad_stream = st
+    return st
 
 
 def _workspace(model, B: int, T: int, device: torch.device) -> Dict[str, Any]:
@@ -67,6 +79,8 @@ def _workspace(model, B: int, T: int, device: torch.device) -> Dict[str, Any]:
         "ln_dg": torch.empty(C, **f32), "ln_db": torch.empty(C, **f32),
         "attn_scratch": torch.empty(native.attention_bwd_scratch_floats(B, T, H), **f32),
     }
+    if device.type == "cuda":
+        ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
     model._ws = {key: ws}
     return ws
 
@@ -105,14 +119,46 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         gemm_fwd(x, lin.weight, out, m=R, n=out_f, k=in_f, bias=lin.bias, act=act, d2=d2, aux=residual,
                  beta=1.0, max_ctas=max_ctas)
 
+    # dgrad and wgrad of a Linear read the same inputs and write different outputs: the wgrad (+ bias column sums)
+    # goes to a side stream and the two GEMMs share the GPU.  Each of them alone leaves most SMs idle in its last
+    # wave (8192 x 768 x 768: 96 tiles on 74 CTA pairs = 1.3 waves), the other one's CTAs take those SMs.
+    fork = _ASYNC_WGRAD and tokens.is_cuda
+    main = torch.cuda.current_stream() if fork else None
+    side = _side_stream(model, dev) if fork else None
+    ev_fork, ev_join = (ws["ev_fork"], ws["ev_join"]) if fork else (None, None)
+
+    def wgrad_pair(dy, x_in, w: nn.Parameter, bias, out_f, in_f, dgrad):
+        """Run ``dgrad()`` on the caller's stream and dW = dy^T x_in (+ db) beside it."""
+        gw = grad_of(w)
+        gb = grad_of(bias) if bias is not None else None
+        if fork:
+            ev_fork.record(main)              # dy, x_in and the gradient slots are ready
+            side.wait_event(ev_fork)
+        dgrad()
+        if fork:
+            torch.cuda.set_stream(side)
+        try:
+            native.gemm(dy, x_in, gw, m=out_f, n=in_f, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
+            if gb is not None:
+                native.colsum_split(dy, gb)
+            if fork:
+                ev_join.record(side)
+        finally:
+            if fork:
+                torch.cuda.set_stream(main)
+        if fork:
+            main.wait_event(ev_join)
+
     def linear_bwd(dy, x_in, lin: nn.Linear, dx_out, *, gelu_pre=None):
-        """dx = dy W (optionally * gelu'(pre)); then dW = dy^T x_in, db = colsum(dy) into the buckets."""
+        """dx = dy W (optionally * gelu'(pre)); dW = dy^T x_in, db = colsum(dy) into the buckets."""
         out_f, in_f = lin.weight.shape
-        if dx_out is not None:
-            native.gemm(dy, wv(lin.weight), dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
-                        act=2 if gelu_pre is not None else 0, max_ctas=max_ctas)
-        native.gemm(dy, x_in, grad_of(lin.weight), m=out_f, n=in_f, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
-        native.colsum_split(dy, grad_of(lin.bias))
+
+        def dgrad():
+            if dx_out is not None:
+                native.gemm(dy, wv(lin.weight), dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
+                            act=2 if gelu_pre is not None else 0, max_ctas=max_ctas)
+
+        wgrad_pair(dy, x_in, lin.weight, lin.bias, out_f, in_f, dgrad)
         ready(lin.weight, lin.bias)
 
     def ln_bwd(dy, x, ln: nn.LayerNorm, mean, rstd, dres, dx):
@@ -142,8 +188,9 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
     dlogits = ws["logits"]
     dxa, dxb = ws["dx"]
     # LM head (tied): dxf = dlogits wte ; dwte = dlogits^T xf  (embedding gradient is added at the very end)
-    native.gemm(dlogits, wv(model.wte.weight), ws["dC"], m=R, n=C, k=V, b_mn=True, max_ctas=max_ctas)
-    native.gemm(dlogits, ws["xf"], grad_of(model.wte.weight), m=V, n=C, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
+    wgrad_pair(dlogits, ws["xf"], model.wte.weight, None, V, C,
+               lambda: native.gemm(dlogits, wv(model.wte.weight), ws["dC"], m=R, n=C, k=V, b_mn=True,
+                                   max_ctas=max_ctas))
     ln_bwd(ws["dC"], x, model.ln_f, ws["meanf"], ws["rstdf"], None, dxa)
     dx = dxa                                   # gradient w.r.t. the block output
     other = dxb

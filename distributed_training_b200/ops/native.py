@@ -132,11 +132,13 @@ _GEMM_WS = {}
 
 
 def _gemm_workspace(device: torch.device) -> torch.Tensor:
-    """Per-device fp32 scratch for split-K partial sums (64 MiB: 8 slices of a 1024 x 2048 output)."""
-    ws = _GEMM_WS.get(device)
+    """fp32 scratch for split-K partial sums (64 MiB: 8 slices of a 1024 x 2048 output), one per (device, stream):
+    GEMMs queued on different streams (dgrad / wgrad of the native models) may run at the same time."""
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    ws = _GEMM_WS.get(key)
     if ws is None:
         ws = torch.empty(16 << 20, dtype=torch.float32, device=device)
-        _GEMM_WS[device] = ws
+        _GEMM_WS[key] = ws
     return ws
 
 
