@@ -154,8 +154,16 @@ class MLP(nn.Module):
         # on ONE stream the next kernel cannot start before the last CTA has exited.  With two independent GEMMs
         # queued the SMs a finishing kernel frees are taken by the other one's CTAs (the tile scheduler is a global
         # counter per stream, so late CTAs simply join).
-        async_w = (_ASYNC_WGRAD and x.is_cuda
-                   and (grad_sink is None or getattr(grad_sink, "supports_async_wgrad", False)))
+        # Modes: "full" (one replica): the two chains never join.  "forkjoin" (several replicas): W_i runs beside D_i
+        # and the streams join before the layer's gradients go to the reducer -- the reduction kernel is then queued
+        # while no GEMM CTA is waiting and takes the SMs that are reserved for it; with "full" the other GEMM's
+        # waiting CTAs take them and the reductions start only when a persistent GEMM ends.
+        mode = None
+        if _ASYNC_WGRAD and x.is_cuda:
+            mode = "full" if grad_sink is None else getattr(grad_sink, "async_wgrad_mode", lambda: None)()
+        async_w = mode is not None
+        forkjoin = mode == "forkjoin"
+        tail_layers = getattr(grad_sink, "TAIL_LAYERS", 1)
         main = torch.cuda.current_stream() if async_w else None
         side = self._wgrad_stream(x.device) if async_w else None
         nbuf = len(ws["dz"]) if async_w else 2
@@ -188,8 +196,10 @@ class MLP(nn.Module):
                     ev_next.record(main)
             if async_w:
                 side.wait_event(ev_dz)
-                if fused_sgd is not None and ev_next is not None:
-                    side.wait_event(ev_next)         # the epilogue below rewrites W_i, which D_i is reading
+                if ev_next is not None and (fused_sgd is not None or (forkjoin and i < tail_layers)):
+                    # fused SGD: the epilogue below rewrites W_i, which D_i is reading.  Tail of a multi-replica
+                    # step: the pieces of W_i and their reductions must not queue behind a full-size D_i
+                    side.wait_event(ev_next)
                 torch.cuda.set_stream(side)
             try:
                 if fused_sgd is not None:
@@ -200,8 +210,7 @@ class MLP(nn.Module):
                                 max_ctas=cap)
                     if on_updated is not None:
                         on_updated([layer.weight])
-                elif (i < getattr(grad_sink, "TAIL_LAYERS", 1)
-                      and getattr(grad_sink, "tail_chunks", lambda p: 1)(layer.weight) > 1):
+                elif i < tail_layers and getattr(grad_sink, "tail_chunks", lambda p: 1)(layer.weight) > 1:
                     # the last wgrads of backward: produce (and reduce) them in row chunks so that only the final
                     # chunk's reduction is exposed; the reductions get more SMs here and the GEMM pieces leave them
                     nch = grad_sink.tail_chunks(layer.weight)
@@ -240,6 +249,8 @@ class MLP(nn.Module):
             finally:
                 if async_w:
                     torch.cuda.set_stream(main)
+            if forkjoin:
+                main.wait_event(ws["ev_w"][i])
             if nxt is not None:
                 dz = nxt
                 ev_dz = ev_next

@@ -73,15 +73,19 @@ class ReplicatedModule(nn.Module):
     (SURVEY §5.4).
     """
 
-    @property
-    def supports_async_wgrad(self) -> bool:
-        """``grad_view`` / ``mark_ready`` may be called with a side stream current (the native MLP can queue its
-        weight gradients there; the reduction is ordered behind whatever stream is current at the call).  Used with
-        one replica only: with two GEMMs always queued, the SMs the backward GEMMs leave to the whole-SM reduction
-        CTAs are taken by the other GEMM's waiting CTAs, and the reductions then start only when a persistent GEMM
-        ends (4 GPUs, profiles/timeline_wide_mlp_n4_async_x8.json: 128 MiB reductions 0.9-1.15 ms instead of 0.48,
-        1.35 ms of them after the last GEMM).  DTB_ASYNC_WGRAD_MULTI=1 turns it on regardless."""
-        return self.comm.world_size == 1 or os.environ.get("DTB_ASYNC_WGRAD_MULTI", "0") == "1"
+    def async_wgrad_mode(self) -> Optional[str]:
+        """How a native model may overlap its weight-gradient GEMMs with the dgrad chain (``grad_view`` / ``mark_ready``
+        may be called with a side stream current; the reduction is ordered behind whatever stream is current).
+        One replica: "full" (the chains never join).  Several replicas: one stream.  Both overlapped forms were
+        measured slower at 4 GPUs because the waiting CTAs of the second GEMM take the SMs that the backward GEMMs
+        leave to the whole-SM reduction CTAs: "full" 10.38 ms/step against 10.26-10.35 (128 MiB reductions 0.9-1.15 ms
+        instead of 0.48, profiles/timeline_wide_mlp_n4_async_x8.json), "forkjoin" (W_i beside D_i, join per layer,
+        reduction queued at the join) 10.92-10.95 against 10.22-10.28.  DTB_ASYNC_WGRAD_MULTI = full | forkjoin turns
+        them on."""
+        if self.comm.world_size == 1:
+            return "full"
+        env = os.environ.get("DTB_ASYNC_WGRAD_MULTI", "0")
+        return {"full": "full", "1": "full", "forkjoin": "forkjoin"}.get(env)
 
     def __init__(self, module: nn.Module, comm: Communicator, bucket_cap_mb: float = 25.0,
                  first_bucket_mb: float = 1.0, init_sync: bool = True,
