@@ -31,6 +31,9 @@ from ..ops import native
 
 #: weight gradients on a side stream beside their dgrad (DTB_ASYNC_WGRAD=0: one stream)
 _ASYNC_WGRAD = os.environ.get("DTB_ASYNC_WGRAD", "1") != "0"
+#: the caller's stream waits for a weight gradient only before a buffer it reads is overwritten
+#: (DTB_ASYNC_WGRAD_DEFER=0: right after queuing it)
+_DEFER_JOIN = os.environ.get("DTB_ASYNC_WGRAD_DEFER", "1") != "0"
 
 
 def _side_stream(model, device: torch.device) -> "torch.cuda.Stream":
@@ -81,6 +84,8 @@ def _workspace(model, B: int, T: int, device: torch.device) -> Dict[str, Any]:
     }
     if device.type == "cuda":
         ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
+        ws["ev_pool_w"] = [torch.cuda.Event() for _ in range(16)]
+        ws["ev_pool_d"] = [torch.cuda.Event() for _ in range(4)]
     model._ws = {key: ws}
     return ws
 
@@ -105,9 +110,16 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         return p.grad
 
     def ready(*params: nn.Parameter) -> None:
-        if grad_sink is not None:
-            for p in params:
-                grad_sink.mark_ready(p)
+        if grad_sink is None:
+            return
+        if deferred:
+            # handed over at the next fork, on the side stream, once that stream is ordered behind this one: a bucket
+            # is reduced behind the stream that is current when its LAST parameter is marked, so every mark has to
+            # come from the stream that also carries the weight gradients
+            pending_ready.extend(params)
+            return
+        for p in params:
+            grad_sink.mark_ready(p)
 
     # a sharded grad_sink gathers each weight inside the forward GEMM that consumes it (gemm_forward) and hands out
     # the transiently gathered matrix wherever else it is read (weight_view: embedding lookup, LM head, dgrad)
@@ -122,31 +134,76 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
     # dgrad and wgrad of a Linear read the same inputs and write different outputs: the wgrad (+ bias column sums)
     # goes to a side stream and the two GEMMs share the GPU.  Each of them alone leaves most SMs idle in its last
     # wave (8192 x 768 x 768: 96 tiles on 74 CTA pairs = 1.3 waves), the other one's CTAs take those SMs.
+    # Two forms: fork-join (the caller's stream waits for the wgrad right away; sharded sinks, whose slot pools are
+    # ordered on the caller's stream) and deferred (plain gradients / ReplicatedModule): the caller's stream goes on
+    # with LayerNorm and attention backward and waits for a wgrad only before one of the buffers it reads is
+    # overwritten, so the weight gradients also run under those latency-bound kernels.
     fork = _ASYNC_WGRAD and tokens.is_cuda
+    deferred = fork and _DEFER_JOIN and (grad_sink is None or hasattr(grad_sink, "async_wgrad_mode"))
     main = torch.cuda.current_stream() if fork else None
     side = _side_stream(model, dev) if fork else None
     ev_fork, ev_join = (ws["ev_fork"], ws["ev_join"]) if fork else (None, None)
+    pending_ready: list = []
+    last_read: Dict[int, Any] = {}          # buffer -> event of the last side-stream kernel that reads it
+    # two rotating pools.  Side-stream events: a re-recorded one stands for a LATER kernel of that in-order stream,
+    # so a stale entry in `last_read` can only wait for more than it needs.  Caller-stream events are consumed by
+    # `side.wait_event` right where they are recorded.
+    pools = {"w": ws.get("ev_pool_w", []), "d": ws.get("ev_pool_d", [])}
+    pool_at = {"w": 0, "d": 0}
 
-    def wgrad_pair(dy, x_in, w: nn.Parameter, bias, out_f, in_f, dgrad):
+    def next_event(kind: str):
+        ev = pools[kind][pool_at[kind] % len(pools[kind])]
+        pool_at[kind] += 1
+        return ev
+
+    def before_write(*bufs: torch.Tensor) -> None:
+        """The caller's stream is about to overwrite ``bufs``: wait for the weight gradients that still read them."""
+        if deferred:
+            for buf in bufs:
+                ev = last_read.pop(buf.data_ptr(), None)
+                if ev is not None:
+                    main.wait_event(ev)
+
+    def wgrad_pair(dy, x_in, w: nn.Parameter, bias, out_f, in_f, dgrad, dx_out=None, mark=True):
         """Run ``dgrad()`` on the caller's stream and dW = dy^T x_in (+ db) beside it."""
         gw = grad_of(w)
         gb = grad_of(bias) if bias is not None else None
         if fork:
             ev_fork.record(main)              # dy, x_in and the gradient slots are ready
             side.wait_event(ev_fork)
+        if dx_out is not None:
+            before_write(dx_out)
         dgrad()
+        ev_d = None
+        if deferred:
+            ev_d = next_event("d")
+            ev_d.record(main)                 # the weight has been read: its bucket may be stepped
         if fork:
             torch.cuda.set_stream(side)
         try:
+            if deferred and pending_ready:    # LayerNorm parameters finished before this fork (side is behind them now)
+                for p in pending_ready:
+                    grad_sink.mark_ready(p)
+                pending_ready.clear()
             native.gemm(dy, x_in, gw, m=out_f, n=in_f, k=R, a_mn=True, b_mn=True, max_ctas=max_ctas)
             if gb is not None:
                 native.colsum_split(dy, gb)
-            if fork:
+            if deferred:
+                ev_w = next_event("w")
+                ev_w.record(side)
+                last_read[dy.data_ptr()] = ev_w
+                last_read[x_in.data_ptr()] = ev_w
+                if grad_sink is not None and mark:
+                    side.wait_event(ev_d)
+                    grad_sink.mark_ready(w)
+                    if bias is not None:
+                        grad_sink.mark_ready(bias)
+            elif fork:
                 ev_join.record(side)
         finally:
             if fork:
                 torch.cuda.set_stream(main)
-        if fork:
+        if fork and not deferred:
             main.wait_event(ev_join)
 
     def linear_bwd(dy, x_in, lin: nn.Linear, dx_out, *, gelu_pre=None):
@@ -158,10 +215,12 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
                 native.gemm(dy, wv(lin.weight), dx_out, m=R, n=in_f, k=out_f, b_mn=True, aux=gelu_pre,
                             act=2 if gelu_pre is not None else 0, max_ctas=max_ctas)
 
-        wgrad_pair(dy, x_in, lin.weight, lin.bias, out_f, in_f, dgrad)
-        ready(lin.weight, lin.bias)
+        wgrad_pair(dy, x_in, lin.weight, lin.bias, out_f, in_f, dgrad, dx_out)
+        if not deferred:
+            ready(lin.weight, lin.bias)
 
     def ln_bwd(dy, x, ln: nn.LayerNorm, mean, rstd, dres, dx):
+        before_write(dx)
         native.layernorm_bwd_bf16grads(dy, x, ln.weight, mean, rstd, dres, dx, grad_of(ln.weight), grad_of(ln.bias),
                                        ws["ln_scratch"])
         ready(ln.weight, ln.bias)
@@ -188,15 +247,17 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
     dlogits = ws["logits"]
     dxa, dxb = ws["dx"]
     # LM head (tied): dxf = dlogits wte ; dwte = dlogits^T xf  (embedding gradient is added at the very end)
+    # (tied weight: handed to the reducer at the very end, after the embedding gradient has been added)
     wgrad_pair(dlogits, ws["xf"], model.wte.weight, None, V, C,
                lambda: native.gemm(dlogits, wv(model.wte.weight), ws["dC"], m=R, n=C, k=V, b_mn=True,
-                                   max_ctas=max_ctas))
+                                   max_ctas=max_ctas), mark=False)
     ln_bwd(ws["dC"], x, model.ln_f, ws["meanf"], ws["rstdf"], None, dxa)
     dx = dxa                                   # gradient w.r.t. the block output
     other = dxb
     for blk, a in zip(reversed(list(model.h)), reversed(ws["blocks"])):
         # x_out = xm + h Wpr^T + b   -> dh (with GELU') ; dWpr, dbpr
         if ws["recompute_gelu"]:
+            before_write(a["h"])
             native.gelu_fwd(a["z"], a["h"])
         linear_bwd(dx, a["h"], blk.mlp_proj, ws["d4C"], gelu_pre=a["z"])
         # z = m Wfc^T + b            -> dm ; dWfc, dbfc
@@ -206,12 +267,19 @@ def gpt2_forward_backward(model, tokens: torch.Tensor, targets: torch.Tensor, gr
         dxm = other
         # xm = x_in + att Wo^T + b   -> datt ; dWo, dbo
         linear_bwd(dxm, a["att"], blk.attn_proj, ws["dC"])
+        before_write(ws["dqkv"])
         native.attention_bwd(a["qkv"], a["att"], ws["dC"], a["lse"], ws["dqkv"], ws["attn_scratch"], H)
         # qkv = a Wqkv^T + b         -> da ; dWqkv, dbqkv
         linear_bwd(ws["dqkv"].view(R, 3 * C), a["a"], blk.attn_qkv, ws["dC"])
         # a = LN1(x_in); residual branch adds dxm
         ln_bwd(ws["dC"], a["x_in"], blk.ln_1, a["mean1"], a["rstd1"], dxm, dx)
         # dx now holds the gradient w.r.t. this block's input; `other` is free again
+    if fork:
+        main.wait_stream(side)     # the LM head's weight gradient is complete: the embedding gradient is added to it
     native.embedding_bwd(dx.view(B, T, C), tokens, grad_of(model.wte.weight), grad_of(model.wpe.weight))
     ready(model.wpe.weight, model.wte.weight)
+    if deferred and grad_sink is not None:      # both streams have joined: the rest goes out from here
+        for p in pending_ready:
+            grad_sink.mark_ready(p)
+        pending_ready.clear()
     return ws["loss"]

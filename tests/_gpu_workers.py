@@ -584,3 +584,59 @@ def collectives_stress(rank, world, port, out_dir, max_mb=1024):
     finally:
         comm.close()
         dist.destroy_process_group()
+
+
+def ddp_native_gpt2(rank, world, port, out_dir):
+    """Native GPT-2 step under DDPStrategy (two-stream backward: weight gradients and every ``mark_ready`` on the side
+    stream) against a single-process fp32 autograd model on the global batch: averaged gradients in the buckets, then
+    two AdamW steps with identical replicas."""
+    from distributed_training_b200.models.gpt2 import GPT2, GPT2Config
+    from distributed_training_b200.parallel.ddp import DDPStrategy
+    from distributed_training_b200.parallel.strategy import OptimizerSpec
+
+    _init(rank, world, port)
+    strategy = DDPStrategy(rank, True, bucket_cap_mb=0.25, first_bucket_mb=0.05)     # several parameters per bucket
+    try:
+        cfg = GPT2Config(vocab_size=1000, n_positions=256, n_embd=128, n_layer=2, n_head=2)
+        torch.manual_seed(100 + rank)                 # rank-dependent init: must be broadcast
+        model = GPT2(cfg, dtype=torch.bfloat16).cuda()
+        wrapped = strategy.prepare_model(model, rank)
+        assert wrapped.native_step
+        ref = GPT2(cfg, dtype=torch.float32).cuda()
+        ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+        g = torch.Generator().manual_seed(5)
+        tok = torch.randint(0, 1000, (2 * world, 256), generator=g).cuda()
+        tgt = torch.randint(0, 1000, (2 * world, 256), generator=g).cuda()
+        mine = slice(2 * rank, 2 * rank + 2)
+        # ---- gradients: the buckets must hold the mean over ranks = the gradient of the global-batch mean loss
+        loss = wrapped.forward_backward(tok[mine], tgt[mine])
+        torch.cuda.synchronize()
+        ref_loss = ref.loss(tok, tgt)
+        ref_loss.backward()
+        losses = _gather_cpu(loss.detach().float().view(1), world)
+        assert abs(float(sum(losses)) / world - float(ref_loss)) < 5e-2
+        bad = []
+        for (name, p), (_, rp) in zip(model.named_parameters(), ref.named_parameters()):
+            got = wrapped.grad_view(p).float().view_as(rp.grad)
+            scale = rp.grad.abs().max().item() + 1e-6
+            err = (got - rp.grad).abs().max().item()
+            if err > 0.08 * scale + 2e-4:
+                bad.append((name, err, scale))
+        assert not bad, bad[:6]
+        # ---- two optimizer steps (AdamW stepped per bucket behind its all-reduce): replicas stay identical
+        opt = strategy.build_optimizer(wrapped, OptimizerSpec("adamw", lr=1e-3, weight_decay=0.01))
+        wrapped.attach_optimizer(opt)
+        for step in range(2):
+            wrapped.forward_backward(tok[mine], tgt[mine])
+            opt.step()
+        torch.cuda.synchronize()
+        flat = torch.cat([p.detach().float().view(-1) for p in model.parameters()])
+        got = _gather_cpu(flat, world)
+        assert all(torch.equal(got[0], t) for t in got), "replicas diverged"
+        assert bool(torch.isfinite(flat).all())
+        strategy.comm.check_errors()
+        torch.save({"ok": True}, os.path.join(out_dir, f"ok{rank}.pt"))
+    finally:
+        if strategy.comm is not None:
+            strategy.comm.close()
+        dist.destroy_process_group()

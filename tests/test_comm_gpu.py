@@ -52,6 +52,12 @@ def test_native_ddp_step_matches_single_process(tmp_path):
     assert all((tmp_path / f"ok{r}.pt").exists() for r in range(w))
 
 
+def test_native_gpt2_ddp_step_matches_single_process(tmp_path):
+    w = 2
+    mp.spawn(G.ddp_native_gpt2, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
+    assert all((tmp_path / f"ok{r}.pt").exists() for r in range(w))
+
+
 def test_native_sharded_strategy_matches_single_process(tmp_path):
     w = _world()
     mp.spawn(G.sharded_native, args=(w, free_port(), str(tmp_path)), nprocs=w, join=True)
