@@ -136,8 +136,8 @@ def main():
         for _ in range(2):
             fn()
         t = timed(fn, 10)
-        emit({"p2p": "all_gather", "bytes_out": n16 * world, "gbs_inbound_per_gpu": round(n16 * (world - 1) / 1e6 / t, 1),
-              "world": world, "nvls": comm.nvls_active})
+        emit({"p2p": "all_gather", "bytes_out": n16 * world,
+              "gbs_inbound_per_gpu": round(n16 * (world - 1) / 1e6 / t, 1), "world": world, "nvls": comm.nvls_active})
     comm.check_errors()
     comm.close()
     dist.destroy_process_group()

@@ -130,7 +130,8 @@ def stage_perf():
         out = torch.empty(m, n, dtype=torch.bfloat16, device="cuda")
         flops = 2.0 * m * n * k
         med, best = _time_ms(lambda: torch.matmul(a, b.t(), out=out))
-        emit(stage="perf", impl="cublas", m=m, n=n, k=k, ms=med, tflops=flops / med / 1e9, best_tflops=flops / best / 1e9)
+        emit(stage="perf", impl="cublas", m=m, n=n, k=k, ms=med, tflops=flops / med / 1e9,
+             best_tflops=flops / best / 1e9)
         for cg, bn in ((1, 128), (1, 256), (2, 256)):
             try:
                 med, best = _time_ms(lambda: native.gemm(a, b, out, m=m, n=n, k=k, cta_pair=cg, tile_n=bn))
@@ -184,8 +185,9 @@ def run_sub(stage, arg=None, timeout=180):
             emit(stage=stage, arg=arg, failed=True, rc=p.returncode, stderr=p.stderr[-1500:])
         return p.returncode == 0, p.stdout
     except subprocess.TimeoutExpired as exc:
-        emit(stage=stage, arg=arg, failed=True, timeout=timeout, partial=(exc.stdout or b"")[-500:].decode(errors="ignore")
-             if isinstance(exc.stdout, bytes) else str(exc.stdout)[-500:])
+        partial = ((exc.stdout or b"")[-500:].decode(errors="ignore") if isinstance(exc.stdout, bytes)
+                   else str(exc.stdout)[-500:])
+        emit(stage=stage, arg=arg, failed=True, timeout=timeout, partial=partial)
         return False, ""
     finally:
         emit(stage=stage, arg=arg, wall_s=round(time.time() - t0, 1))
@@ -208,7 +210,8 @@ def driver():
             seen.add(tag)
             if not rec["ok"]:
                 bad.add(tag)
-    all_tags = [f"{a},{b},{cg},{bn}" for a, b, (cg, bn) in itertools.product((0, 1), (0, 1), ((1, 128), (1, 256), (2, 256)))]
+    all_tags = [f"{a},{b},{cg},{bn}"
+                for a, b, (cg, bn) in itertools.product((0, 1), (0, 1), ((1, 128), (1, 256), (2, 256)))]
     if not ok_all:   # a variant crashed/hung: re-run each remaining one on its own
         for tag in all_tags:
             if tag not in seen or tag in bad:

@@ -69,7 +69,8 @@ def main():
         from distributed_training_b200.parallel.strategy import OptimizerSpec
 
         model = (MLP(8192, 8192, 8192, 8, dtype=torch.bfloat16) if is_mlp else
-                 GPT2(GPT2Config(n_embd=c["n_embd"], n_layer=c["n_layer"], n_head=c["n_head"]), dtype=torch.bfloat16)).cuda()
+                 GPT2(GPT2Config(n_embd=c["n_embd"], n_layer=c["n_layer"], n_head=c["n_head"]),
+                      dtype=torch.bfloat16)).cuda()
         strategy = DDPStrategy(local, True) if ns.strategy == "ddp" else FSDPStrategy(True)
         wrapped = strategy.prepare_model(model, local)
         spec = OptimizerSpec(opt_name, lr=1e-4, weight_decay=0.0 if opt_name == "sgd" else 0.1)
@@ -133,7 +134,8 @@ def main():
         # exactly what the reference's strategies do (ddp_strategy.py:18, fsdp_strategy.py:20-26)
         wrapped = DDP(model, device_ids=[local]) if ns.strategy == "ddp" else FSDP(model, device_id=local)
         params = wrapped.parameters()
-        opt = torch.optim.SGD(params, lr=1e-4) if opt_name == "sgd" else torch.optim.AdamW(params, lr=1e-4, weight_decay=0.1)
+        opt = (torch.optim.SGD(params, lr=1e-4) if opt_name == "sgd"
+               else torch.optim.AdamW(params, lr=1e-4, weight_decay=0.1))
 
         def step(i):
             opt.zero_grad()
@@ -141,7 +143,8 @@ def main():
             if is_mlp or ns.ref_loss:
                 loss = torch.nn.functional.cross_entropy(out, y)
             else:       # [B, V, T] -> [B*T, V] fp32
-                loss = torch.nn.functional.cross_entropy(out.transpose(1, 2).float().reshape(-1, out.shape[1]), y.view(-1))
+                flat = out.transpose(1, 2).float().reshape(-1, out.shape[1])
+                loss = torch.nn.functional.cross_entropy(flat, y.view(-1))
             loss.backward()
             opt.step()
 

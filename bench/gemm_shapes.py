@@ -20,7 +20,8 @@ rows = []
 for name, (m, n, k) in {"qkv": (R, 3*C, C), "proj": (R, C, C), "fc": (R, 4*C, C), "proj2": (R, C, 4*C)}.items():
     x, w, b = torch.randn(m, k, **bf), torch.randn(n, k, **bf) * 0.02, torch.randn(n, **bf)
     out, z, res = torch.empty(m, n, **bf), torch.empty(m, n, **bf), torch.randn(m, n, **bf)
-    dy = torch.randn(m, n, **bf); dx = torch.empty(m, k, **bf); dw = torch.empty(n, k, **bf); pre = torch.randn(m, k, **bf)
+    dy, dx = torch.randn(m, n, **bf), torch.empty(m, k, **bf)
+    dw, pre = torch.empty(n, k, **bf), torch.randn(m, k, **bf)
     r = {"layer": name, "mode": os.environ.get("DTB_GEMM_DIRECT_EPILOGUE", "0"),
          "fwd_plain": t(lambda: native.gemm(x, w, out, m=m, n=n, k=k)),
          "fwd_bias": t(lambda: native.gemm(x, w, out, m=m, n=n, k=k, bias=b)),

@@ -2,7 +2,8 @@
 GPT-2 small batch 8x1024).  Two uses:
 
     python bench/kernel_zoo.py                 # CUDA-event time per kernel (L2 flushed before each), JSON lines
-    ncu --set full --clock-control none --import-source on --profile-from-start off -o zoo python bench/kernel_zoo.py --ncu
+    ncu --set full --clock-control none --import-source on --profile-from-start off -o zoo \
+        python bench/kernel_zoo.py --ncu
 
 With ``--ncu`` each kernel runs once inside a cudaProfilerStart/Stop window (after an unprofiled warm-up), so the
 report contains exactly one instance of every kernel and nothing from torch.
@@ -115,7 +116,8 @@ def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--ncu", action="store_true")
     ap.add_argument("--iters", type=int, default=10)
-    ap.add_argument("--only", default="", help="comma-separated substrings: run only the kernels whose name matches one")
+    ap.add_argument("--only", default="",
+                    help="comma-separated substrings: run only the kernels whose name matches one")
     ns = ap.parse_args()
     native.require()
     peaks = json.loads((Path(__file__).resolve().parent.parent / "MEASURED_PEAKS.json").read_text()) \

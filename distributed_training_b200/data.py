@@ -218,7 +218,8 @@ class ShardedLoader:
         self.num_workers = max(int(num_workers), 0)
         self.prefetch = max(int(prefetch), 1)
         self._copy_stream = torch.cuda.Stream(self.device) if cuda else None
-        self._staging: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None] * (self.prefetch + 1 if self.num_workers else 2)
+        slots = self.prefetch + 1 if self.num_workers else 2
+        self._staging: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None] * slots
         self._pool: Optional[ThreadPoolExecutor] = None
         if device_gather is None:
             device_gather = cuda and hasattr(dataset, "tensors") and _native_available()

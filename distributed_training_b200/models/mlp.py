@@ -22,7 +22,8 @@ from torch import nn
 from ..ops import native
 
 _FUSED_COLSUM = os.environ.get("DTB_FUSED_COLSUM", "1") != "0"
-#: weight gradients on a side stream so that consecutive GEMMs fill each other's last wave (DTB_ASYNC_WGRAD=0: one stream)
+#: weight gradients on a side stream so that consecutive GEMMs fill each other's last wave
+#: (DTB_ASYNC_WGRAD=0: one stream)
 _ASYNC_WGRAD = os.environ.get("DTB_ASYNC_WGRAD", "1") != "0"
 
 
@@ -238,7 +239,8 @@ class MLP(nn.Module):
                         native.colsum_split(dz[:, :out_f], grad_of(layer.bias), ldx=dz.shape[1])
                 if grad_sink is not None:
                     if async_w and ev_next is not None:
-                        side.wait_event(ev_next)     # the reducer may rewrite W_i (fused reduce + SGD): D_i must be done
+                        # the reducer may rewrite W_i (fused reduce + SGD): D_i must be done
+                        side.wait_event(ev_next)
                     grad_sink.mark_ready(layer.weight)
                     if layer.bias is not None:
                         grad_sink.mark_ready(layer.bias)

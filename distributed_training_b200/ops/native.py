@@ -230,7 +230,8 @@ def gemm_allgather(a: torch.Tensor, b_full: torch.Tensor, out: torch.Tensor, pee
     return out
 
 
-def make_gather_args(peer_shard_ptrs: Sequence[int], flags: torch.Tensor, rank: int, rows_per_rank: int) -> "GatherArgs":
+def make_gather_args(peer_shard_ptrs: Sequence[int], flags: torch.Tensor, rank: int,
+                     rows_per_rank: int) -> "GatherArgs":
     """The per-weight constant half of a ``gemm_allgather`` call (build once, pass as ``gather_args``)."""
     g = GatherArgs()
     for r, ptr in enumerate(peer_shard_ptrs):
@@ -541,7 +542,8 @@ def comm_barrier(desc: CommDesc, channel: int = 0, stream: Optional[int] = None)
     _ok(lib().dtb_comm_barrier(C.byref(desc), channel, _stream(stream)))
 
 
-def comm_broadcast(desc: CommDesc, offset: int, nbytes: int, root: int, max_ctas: int = 0, channel: int = 0, stream: Optional[int] = None):
+def comm_broadcast(desc: CommDesc, offset: int, nbytes: int, root: int, max_ctas: int = 0, channel: int = 0,
+                   stream: Optional[int] = None):
     _ok(lib().dtb_comm_broadcast(C.byref(desc), C.c_size_t(offset), C.c_size_t(nbytes), root,
                                  _cta_arg(max_ctas, channel), _stream(stream)))
 

@@ -247,7 +247,8 @@ class NativeShardedModule(nn.Module):
         self._access.append((id(sw.param), kind))
         return i
 
-    def _take_slot(self, pool: Dict[int, List[_Slot]], sw: _ShardedWeight, index: int, for_index: int) -> Optional[_Slot]:
+    def _take_slot(self, pool: Dict[int, List[_Slot]], sw: _ShardedWeight, index: int,
+                   for_index: int) -> Optional[_Slot]:
         """A slot of ``sw``'s size class whose content is no longer needed: unowned first, else the one whose
         (planned) use lies furthest in the past.  Slots stamped at or after ``index`` are in use / prefetched for
         later and are not taken (returns None then, unless this is the access that needs it now)."""

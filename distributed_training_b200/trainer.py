@@ -425,7 +425,8 @@ def training_config_from(cfg: Any) -> TrainingConfig:
         bucket_cap_mb=train.get("bucket_cap_mb", 25),
         save_optimizer=bool(train.get("save_optimizer", False)),
         log_every=cfg.logging.get("log_every", 50) if "logging" in cfg else 50,
-        metrics_file=str(cfg.logging.get("metrics_file")) if "logging" in cfg and cfg.logging.get("metrics_file") else None,
+        metrics_file=(str(cfg.logging.get("metrics_file"))
+                      if "logging" in cfg and cfg.logging.get("metrics_file") else None),
     )
 
 

@@ -40,7 +40,8 @@ class KernelTimeline:
 
     DEFAULT = ("gemm", "gemm_allgather", "colsum", "colsum_split", "cross_entropy_fwd_bwd", "mse_fwd_bwd",
                "attention_fwd", "attention_bwd", "layernorm_fwd", "layernorm_bwd", "embedding_fwd", "embedding_bwd",
-               "multi_tensor_sgd", "multi_tensor_adamw", "cast_f32_to_bf16", "take_f32_to_bf16", "mean_f32", "shard_update", "comm_all_reduce_avg", "comm_all_reduce_sgd", "comm_all_reduce_ce",
+               "multi_tensor_sgd", "multi_tensor_adamw", "cast_f32_to_bf16", "take_f32_to_bf16", "mean_f32",
+               "shard_update", "comm_all_reduce_avg", "comm_all_reduce_sgd", "comm_all_reduce_ce",
                "comm_all_gather", "comm_reduce_scatter_avg", "comm_rs_optim", "comm_broadcast")
 
     def __init__(self, names=DEFAULT) -> None:

@@ -1,4 +1,5 @@
-"""``python src/playground/ddp_script.py`` — the from-scratch DDP demo (/root/reference/src/playground/ddp_script.py:1-260)."""
+"""``python src/playground/ddp_script.py`` — the from-scratch DDP demo
+(/root/reference/src/playground/ddp_script.py:1-260)."""
 import os
 import sys
 

@@ -46,7 +46,8 @@ def collectives(rank, world, port, out_dir, nvls="auto"):
         dev = comm.device
         comm.reserve(1 << 20)
         if nvls == "1" and not comm.multicast:
-            torch.save({"ok": True, "skipped": "no multicast support on this box"}, os.path.join(out_dir, f"ok{rank}.pt"))
+            torch.save({"ok": True, "skipped": "no multicast support on this box"},
+                       os.path.join(out_dir, f"ok{rank}.pt"))
             return
         assert comm.nvls_active == (comm.multicast and (nvls == "1" or (nvls == "auto" and world >= 4)))
         # ---- all-reduce: one-shot and two-shot sizes, both dtypes, repeated (flag reuse) ----

@@ -45,4 +45,5 @@ def test_wide_mlp_layout():
                torch.empty(0, dtype=torch.bfloat16).new_empty((8192,), device="meta")]
     plans = plan_buckets(ps)
     weight_buckets = [p for p in plans if any(ps[i].dim() == 2 for i in p.param_indices)]
-    assert len(weight_buckets) == 8 and all(len([i for i in p.param_indices if ps[i].dim() == 2]) == 1 for p in weight_buckets)
+    assert len(weight_buckets) == 8
+    assert all(len([i for i in p.param_indices if ps[i].dim() == 2]) == 1 for p in weight_buckets)

@@ -69,7 +69,8 @@ def test_main_decorator_creates_run_dir_and_dumps(tmp_path, monkeypatch):
     run = tmp_path / "myrun"
     assert Path(seen["cwd"]).resolve() == run.resolve()          # hydra.job.chdir: True
     assert seen["log"] == str(run / "train.log")
-    assert yaml.safe_load((run / ".hydra" / "overrides.yaml").read_text()) == ["train.batch_size=8", "hydra.run.dir=myrun"]
+    saved = yaml.safe_load((run / ".hydra" / "overrides.yaml").read_text())
+    assert saved == ["train.batch_size=8", "hydra.run.dir=myrun"]
     dumped = yaml.safe_load((run / ".hydra" / "config.yaml").read_text())
     assert dumped["train"]["batch_size"] == 8 and "hydra" not in dumped
     assert os.getcwd() == str(tmp_path)                             # restored

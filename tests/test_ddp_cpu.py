@@ -79,8 +79,9 @@ def test_trainer_end_to_end_save_cadence_and_resume(tmp_path):
 
 def test_trainer_fsdp_strategy_on_cpu(tmp_path):
     snap = tmp_path / "snap_fsdp.pt"
-    overrides = [f"train.snapshot_path={snap}", "train.dataset_size=128", "train.batch_size=16", "train.dataset=teacher",
-                 "train.total_epochs=2", "train.device=cpu", "train.parallel_strategy=fsdp", "model=mlp_toy",
+    overrides = [f"train.snapshot_path={snap}", "train.dataset_size=128", "train.batch_size=16",
+                 "train.dataset=teacher", "train.total_epochs=2", "train.device=cpu",
+                 "train.parallel_strategy=fsdp", "model=mlp_toy",
                  "train.optimizer=adamw", "train.learning_rate=0.01", f"hydra.run.dir={tmp_path}/runf"]
     res = _run_trainer(tmp_path, 2, overrides, "fsdp")
     ckpt = torch.load(snap, weights_only=False)

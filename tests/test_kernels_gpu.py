@@ -18,7 +18,8 @@ def _bf16(*shape, scale=1.0, seed=0):
 
 
 def test_library_loaded_on_gpu_box():
-    assert native.available(), "libdtb200.so must be present on a GPU machine (python -m distributed_training_b200._native)"
+    assert native.available(), \
+        "libdtb200.so must be present on a GPU machine (python -m distributed_training_b200._native)"
     assert native.lib().dtb_version() >= 100
 
 
@@ -261,7 +262,8 @@ def test_layernorm_bwd_bf16_param_grads_match_fp32_path():
     dx32, dg32, db32 = torch.empty_like(x), torch.empty(cols, device=DEV), torch.empty(cols, device=DEV)
     native.layernorm_bwd(dy, x, g, mean, rstd, None, dx32, dg32, db32, scratch)
     dx16 = torch.empty_like(x)
-    dg16, db16 = torch.empty(cols, device=DEV, dtype=torch.bfloat16), torch.empty(cols, device=DEV, dtype=torch.bfloat16)
+    dg16 = torch.empty(cols, device=DEV, dtype=torch.bfloat16)
+    db16 = torch.empty(cols, device=DEV, dtype=torch.bfloat16)
     native.layernorm_bwd_bf16grads(dy, x, g, mean, rstd, None, dx16, dg16, db16, scratch)
     assert torch.equal(dx16, dx32)
     assert torch.equal(dg16, dg32.to(torch.bfloat16)) and torch.equal(db16, db32.to(torch.bfloat16))

@@ -21,7 +21,8 @@ pytestmark = pytest.mark.skipif(not (ROOT / "baseline" / "_ref" / "src").exists(
 def _run_ref(code: str, port: int) -> str:
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0",
                PYTHONPATH=str(ROOT))
-    prelude = "import sys; sys.path.insert(0, %r)\nfrom baseline.ref_loader import load_reference\nref = load_reference()\n" % str(ROOT)
+    prelude = ("import sys; sys.path.insert(0, %r)\nfrom baseline.ref_loader import load_reference\n"
+               "ref = load_reference()\n") % str(ROOT)
     out = subprocess.run([sys.executable, "-c", prelude + textwrap.dedent(code)], env=env, capture_output=True,
                          text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-3000:]
@@ -104,7 +105,8 @@ def test_reference_loss_is_identically_zero_quirk(tmp_path):
 
     cfg = TrainingConfig(1, 5, 32, 0.1, tmp_path / "s.pt", device="cpu", loss="cross_entropy")
     trainer = Trainer(torch.nn.Linear(20, 1), prepare_dataloader(MyTrainDataset(64), 32), None, cfg,
-                      DistributedEnvironment("cpu"), strategy=DDPStrategy(0, False, comm=SingleProcessComm(torch.device("cpu"))))
+                      DistributedEnvironment("cpu"),
+                      strategy=DDPStrategy(0, False, comm=SingleProcessComm(torch.device("cpu"))))
     before = trainer.model.module.weight.detach().clone()
     trainer.train(1)
     assert float(trainer.last_loss) == 0.0 and torch.equal(before, trainer.model.module.weight.detach())
