@@ -15,8 +15,8 @@ roadmap.  This implementation follows the roadmap's intent:
 * when the last gradient of a unit lands, the unit's flat gradient is
   reduce-scattered (mean) to the owning ranks, overlapping the remaining
   backward; with the fused optimizer the shard update runs right there
-  (``csrc/fused/rs_optim.cu`` does reduce-scatter + AdamW in one kernel on
-  B200);
+  (``dtb_comm_rs_optim`` in ``csrc/comm/collectives.cu`` does reduce-scatter +
+  AdamW in one kernel on B200: the native path, ``sharded_native.py``);
 * ``state_dict()`` is a collective that returns the full, *unprefixed*
   parameter names (what FSDP's FULL_STATE_DICT produces), so snapshots load
   into a bare model, into the DDP strategy, or into the reference.
