@@ -588,3 +588,70 @@ def test_gemm_split_k(split, a_mn, b_mn):
     one = torch.empty_like(out)
     native.gemm(a, b, one, m=m, n=n, k=k, a_mn=a_mn, b_mn=b_mn, bias=bias, aux=res, beta=0.5, alpha=0.25, split_k=1)
     assert torch.allclose(out.float(), one.float(), atol=0.13, rtol=2e-2)
+
+
+# ------------------------------------------------------------- loss curves
+def test_loss_curve_wide_mlp_north_star_shape_matches_torch_baseline():
+    """BASELINE.json config 2 at full size (8 x 8192, batch 4096, bf16, SGD): the native step and the plain-torch
+    model of the reference arm start from the same weights, see the same batches and must trace the same loss curve."""
+    from baseline.models import wide_mlp_torch
+    from distributed_training_b200.models.mlp import wide_mlp
+    from distributed_training_b200.optim import FusedSGD
+
+    torch.manual_seed(0)
+    ours = wide_mlp().to(DEV)
+    ref = wide_mlp_torch().to(DEV)
+    linears = [m for m in ref if isinstance(m, torch.nn.Linear)]
+    with torch.no_grad():
+        for mine, theirs in zip(ours.layers, linears):
+            theirs.weight.copy_(mine.weight)
+            theirs.bias.copy_(mine.bias)
+    lr = 0.05
+    opt = FusedSGD(ours.parameters(), lr=lr)
+    ropt = torch.optim.SGD(ref.parameters(), lr=lr)
+    g = torch.Generator().manual_seed(3)
+    curve, rcurve = [], []
+    for step in range(6):
+        x = torch.randn(4096, 8192, generator=g).to(torch.bfloat16).to(DEV)
+        y = torch.randint(0, 8192, (4096,), generator=g).to(DEV)
+        curve.append(float(ours.forward_backward(x, y)))
+        opt.step()
+        ropt.zero_grad(set_to_none=True)
+        rl = F.cross_entropy(ref(x).float(), y)
+        rl.backward()
+        ropt.step()
+        rcurve.append(float(rl))
+    assert all(abs(a - b) < 2e-2 for a, b in zip(curve, rcurve)), (curve, rcurve)
+    # the weights moved (bf16 SGD at this lr) and moved the same way
+    w0, r0 = ours.layers[-1].weight.float(), linears[-1].weight.float()
+    assert float((w0 - r0).abs().max()) < 2e-2 * float(r0.abs().max()) + 1e-4
+
+
+def test_loss_curve_gpt2_native_matches_eager_fp32():
+    """A 4-layer GPT-2 of GPT-2 small's width at seq 1024: native step + fused AdamW (fp32 master weights) against
+    eager fp32 autograd + torch AdamW over the same batches."""
+    from distributed_training_b200.models.gpt2 import GPT2, GPT2Config
+    from distributed_training_b200.optim import FusedAdamW
+
+    torch.manual_seed(0)
+    cfg = GPT2Config(n_layer=4)
+    model = GPT2(cfg, dtype=torch.bfloat16).to(DEV)
+    ref = GPT2(cfg, dtype=torch.float32).to(DEV)
+    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    opt = FusedAdamW(model.parameters(), lr=3e-4, weight_decay=0.1, master_weights=True)
+    ropt = torch.optim.AdamW(ref.parameters(), lr=3e-4, weight_decay=0.1)
+    g = torch.Generator().manual_seed(11)
+    batches = [torch.randint(0, cfg.vocab_size, (4, 1025), generator=g).to(DEV) for _ in range(2)]
+    curve, rcurve = [], []
+    for step in range(6):
+        t = batches[step % 2]
+        tok, tgt = t[:, :-1].contiguous(), t[:, 1:].contiguous()
+        curve.append(float(model.forward_backward(tok, tgt)))
+        opt.step()
+        ropt.zero_grad(set_to_none=True)
+        rl = ref.loss(tok, tgt)
+        rl.backward()
+        ropt.step()
+        rcurve.append(float(rl))
+    assert rcurve[-1] < rcurve[0] - 0.05, rcurve                     # the reference is learning (memorising 2 batches)
+    assert all(abs(a - b) < 4e-2 for a, b in zip(curve, rcurve)), (curve, rcurve)
