@@ -23,7 +23,7 @@ WATCH = ["UTCHMMA", "UTMALDG", "UTMASTG", "UBLKCP", "UBLKRED", "LDTM", "STTM", "
          "SYNCS.PHASECHK", "ELECT", "MUFU.EX2", "LDGMC", "REDG", "STAS", "UCGABAR", "LDG.E.128", "STG.E.128", "STS.128",
          "LDG.E.ENL2.256", "STG.E.ENL2.256", "SHFL", "ATOMG", "MEMBAR", "CCTL"]
 KEEP = ["allreduce_nvls_kernel", "broadcast_nvls_kernel", "allgather_nvls_kernel", "bwd_ws_kernel", "bwd_fused_kernel",
-        "gather_rows_kernel"]
+        "gather_rows_kernel", "ce_stream_kernel", "fwd_lazy_kernel"]
 
 
 def main() -> None:
