@@ -76,9 +76,15 @@ class MLP(nn.Module):
                 "dz": [torch.empty(rows, max(self.dims[1:-1] or [8]), **bf) for _ in range(3 if n > 2 else 2)],
                 "row_loss": torch.empty(rows, dtype=torch.float32, device=device),
                 "loss": torch.empty((), dtype=torch.float32, device=device),
-                # fp32 bias-gradient accumulators the dgrad epilogues add into (zero between steps)
-                "bsum": [torch.zeros(self.dims[i + 1], dtype=torch.float32, device=device) for i in range(n - 1)],
             }
+            # fp32 bias-gradient accumulators the dgrad epilogues add into: views of one buffer that is cleared with
+            # one launch at the start of every backward (a step that died half-way must not leave sums behind)
+            widths = [(self.dims[i + 1] + 7) // 8 * 8 for i in range(n - 1)]
+            ws["bsum_flat"] = torch.zeros(max(sum(widths), 8), dtype=torch.float32, device=device)
+            ws["bsum"], at = [], 0
+            for i, w in enumerate(widths):
+                ws["bsum"].append(ws["bsum_flat"][at:at + self.dims[i + 1]])
+                at += w
             if device.type == "cuda":
                 ws["ev_d"] = [torch.cuda.Event() for _ in range(n)]      # dz_i complete (dgrad stream)
                 ws["ev_w"] = [torch.cuda.Event() for _ in range(n)]      # layer i's gradients queued (wgrad stream)
@@ -170,6 +176,8 @@ class MLP(nn.Module):
         nbuf = len(ws["dz"]) if async_w else 2
         dz = ws["logits"]
         cap = max_ctas
+        if n > 1 and any(self._fuse_bias_grad(i, self.dims[i + 2]) for i in range(n - 1)):
+            ws["bsum_flat"].zero_()
         ev_dz = None            # dz_i (and layer i's bias-gradient sums) are complete on the dgrad stream
         if async_w:
             ev_dz = ws["ev_d"][n - 1]
