@@ -161,10 +161,10 @@ class MLP(nn.Module):
         # on ONE stream the next kernel cannot start before the last CTA has exited.  With two independent GEMMs
         # queued the SMs a finishing kernel frees are taken by the other one's CTAs (the tile scheduler is a global
         # counter per stream, so late CTAs simply join).
-        # Modes: "full" (one replica): the two chains never join.  "forkjoin" (several replicas): W_i runs beside D_i
-        # and the streams join before the layer's gradients go to the reducer -- the reduction kernel is then queued
-        # while no GEMM CTA is waiting and takes the SMs that are reserved for it; with "full" the other GEMM's
-        # waiting CTAs take them and the reductions start only when a persistent GEMM ends.
+        # Modes (the grad sink decides, ``ReplicatedModule.async_wgrad_mode``): "full" = the two chains never join (one
+        # replica); None = one stream (several replicas: a second queued GEMM takes the SMs that are left to the
+        # whole-SM reduction CTAs, measured slower); "forkjoin" = W_i beside D_i with a join per layer (opt-in, also
+        # measured slower for the same reason).
         mode = None
         if _ASYNC_WGRAD and x.is_cuda:
             mode = "full" if grad_sink is None else getattr(grad_sink, "async_wgrad_mode", lambda: None)()
